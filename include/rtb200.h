@@ -1,0 +1,144 @@
+/* rtb200.h -- C ABI of the B200-native replacement for the reference's render path.
+ *
+ * The reference (antoinedesbois/Ray-Tracer-Rust) has no FFI or plugin interface: the hot
+ * path is reached by the in-binary call `render(scene)` (src/main.rs:361 -> src/main.rs:242).
+ * The entry points below are what a Rust `extern "C"` block in that crate would bind to
+ * replace that call and the constructors feeding it; each one names the reference
+ * interface it stands in for.  Plain pointers and sizes only; no CUDA or torch types.
+ *
+ * Conventions: every function returning int returns RTB_OK (0) or a negative rtb_status;
+ * rtb_last_error() gives the message for the calling thread.  All host buffers are owned
+ * by the caller and only borrowed for the duration of the call.  A handle is bound to
+ * one CUDA device and is not re-entrant; distinct handles are independent.
+ * There is no CPU fallback: without a usable CUDA device every compute call fails.
+ */
+#ifndef RTB200_H
+#define RTB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    RTB_OK = 0,
+    RTB_ERR_ARG = -1,      /* bad argument */
+    RTB_ERR_CUDA = -2,     /* CUDA runtime error (message in rtb_last_error) */
+    RTB_ERR_STATE = -3,    /* call order: e.g. render before rtb_scene_set_samples */
+    RTB_ERR_IO = -4,       /* file could not be read / written */
+    RTB_ERR_LIMIT = -5     /* scene exceeds a built-in limit (e.g. BVH depth > stack) */
+} rtb_status;
+
+/* Opaque device-resident scene: triangles (SoA float4), BVH, light, sample table.
+ * Replaces `Scene` (src/tracer/utils/scene.rs:6-12) + `BoundingVolumeHierarchy`
+ * (src/tracer/utils/bounding_volume_hierarchy.rs:145-148). */
+typedef struct rtb_scene rtb_scene;
+
+/* What `main` hands to Scene{..}/BoundingVolumeHierarchy::new (src/main.rs:324-358). */
+typedef struct {
+    uint32_t n_tris;          /* primitives in the reference's order: OBJ faces in argv order, ground last */
+    const float* verts;       /* n_tris * 9: v0.xyz v1.xyz v2.xyz (Triangle::new args, triangle.rs:22) */
+    const float* colors;      /* n_tris * 3: linear RGB (Color, color.rs:4-8) */
+    const int32_t* tie_rank;  /* optional n_tris: order used ONLY to break exact-equal-distance ties between two
+                                 primitives (larger wins; the reference's rule is "later leaf in its tree",
+                                 bounding_volume_hierarchy.rs:123-130).  NULL: computed on the device by
+                                 replaying the reference's pairing (n_tris <= RTB_TIE_RANK_MAX_TRIS), else index. */
+    float light[9];           /* area-light triangle; only primitives[0] is sampled (light.rs:10-14) */
+    int32_t device;           /* CUDA device ordinal */
+} rtb_scene_desc;
+
+#define RTB_TIE_RANK_MAX_TRIS 65536u
+
+/* Per-frame parameters: the compile-time constants of src/main.rs:38-40 and the literals of
+ * src/main.rs:349-356 made explicit, plus the multi-GPU band ownership. */
+typedef struct {
+    uint32_t width, height;       /* Scene.width/height (src/main.rs:350-351) */
+    uint32_t nb_ray;              /* NB_RAY, rays per pixel (src/main.rs:38) */
+    uint32_t nb_light_sample;     /* NB_LIGHT_SAMPLE (src/main.rs:39) */
+    float eye[3], look_at[3], up[3], distance;   /* Camera::new args (camera.rs:17-20) */
+    /* Image rows are grouped in bands of band_rows rows; band b belongs to rank (b % world).
+     * world == 1 (or 0) renders the whole frame.  Owned bands are stored compactly, in
+     * increasing band order, in the output buffer (see rtb_owned_rows). */
+    uint32_t band_rows, rank, world;
+    uint32_t flags;               /* RTB_FLAG_* */
+} rtb_render_params;
+
+#define RTB_FLAG_COUNTERS 1u      /* also count AABB / triangle tests (slower instrumented kernel) */
+
+typedef struct {
+    uint64_t primary_rays, primary_hits, shadow_rays, shadow_occluded;
+    uint64_t box_tests, tri_tests;   /* only with RTB_FLAG_COUNTERS, else 0 */
+    float kernel_ms;                 /* device time of the trace kernel(s) of this call (CUDA events) */
+    uint32_t launches;               /* kernels launched by this call */
+} rtb_stats;
+
+typedef struct {
+    uint32_t n_tris, n_nodes, max_depth, ploc_iterations;
+    float sah_cost;                  /* surface-area-heuristic cost of the built tree (diagnostic) */
+    float build_ms;
+} rtb_scene_info;
+
+/* --- replaces BoundingVolumeHierarchy::new + Scene{..} (src/main.rs:349-358): uploads the
+ *     primitives, flattens them to SoA float4, builds the BVH on the device. */
+int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out);
+void rtb_scene_destroy(rtb_scene* scene);
+int rtb_scene_get_info(const rtb_scene* scene, rtb_scene_info* info);
+
+/* --- replaces the random_samples table of render() (src/main.rs:253,260-265): n_pairs (u,v)
+ *     pairs in [0,1).  Must be called before any render.  The table is an explicit input
+ *     because the reference draws it from an OS-seeded RNG. */
+int rtb_scene_set_samples(rtb_scene* scene, const float* samples, uint32_t n_pairs);
+
+/* --- replaces render(scene) up to (not including) the PNG save (src/main.rs:242-310):
+ *     renders the rows owned by (rank, world) and copies them to the HOST buffer rgb8
+ *     (rtb_owned_rows(...) * width * 3 bytes, row-major RGB8, bands in increasing order).
+ *     Blocking.  stats may be NULL. */
+int rtb_render(rtb_scene* scene, const rtb_render_params* params, uint8_t* rgb8, rtb_stats* stats);
+
+/* Same, but the output stays on the device: d_rgb8 is a device pointer on the scene's device,
+ * cuda_stream a cudaStream_t (NULL = default stream).  Asynchronous: returns after the launch.
+ * This is the form the multi-GPU gather uses (the buffer is an NCCL send buffer). */
+int rtb_render_device(rtb_scene* scene, const rtb_render_params* params, void* d_rgb8, void* cuda_stream);
+
+/* --- replaces render_pixel (src/main.rs:180-240) for an explicit list of n_pix (px,py) pairs;
+ *     all outputs are HOST arrays indexed by list position, any may be NULL:
+ *     rgb_lin 3 floats (the returned Color), rgb8 3 bytes (Color::to_rgba, color.rs:26-33),
+ *     hit_count = primary rays of the pixel that hit, prim0/t0 = primitive and distance of ray 0
+ *     (-1 / 0 on a miss) i.e. HitInfo.distance (bounding_volume_hierarchy.rs:150-156). */
+int rtb_render_pixels(rtb_scene* scene, const rtb_render_params* params, const uint32_t* pixels, uint64_t n_pix,
+                      float* rgb_lin, uint8_t* rgb8, uint8_t* hit_count, int32_t* prim0, float* t0,
+                      rtb_stats* stats);
+
+/* Rows owned by (rank, world) for a frame of `height` rows in bands of band_rows. */
+uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint32_t world);
+
+/* Rank 0 after the gather: d_staged holds world consecutive per-rank buffers (each padded to
+ * stride_bytes); writes the row-major frame to d_frame.  Device pointers, asynchronous.
+ * Replaces the put_pixel placement of src/main.rs:291-295. */
+int rtb_deinterleave_bands(int32_t device, const void* d_staged, uint64_t stride_bytes, void* d_frame,
+                           uint32_t width, uint32_t height, uint32_t band_rows, uint32_t world, void* cuda_stream);
+
+/* --- host-side entry points kept from main.rs --- */
+
+/* import_obj (src/main.rs:114-149): `v`/`f` lines only, split on single spaces, bare 1-based
+ * indices.  *verts_out is malloc'ed n*9 floats (free with rtb_free).  An unreadable path is
+ * NOT an error for the reference (prints "Not a valid path" and yields no triangles); here it
+ * returns RTB_ERR_IO with *n_out = 0 so the caller can print and continue. */
+int rtb_import_obj(const char* path, float** verts_out, uint32_t* n_out);
+void rtb_free(void* p);
+
+/* Deterministic stand-in for thread_rng (src/main.rs:260-265): SplitMix64(seed) stream, value j =
+ * top 24 bits * 2^-24; out holds 2*n_pairs floats. */
+void rtb_fill_samples(uint64_t seed, uint32_t n_pairs, float* out);
+
+/* img.save(fout, image::PNG) (src/main.rs:312-315): RGB8, row-major. */
+int rtb_write_png(const char* path, const uint8_t* rgb8, uint32_t width, uint32_t height);
+
+const char* rtb_last_error(void);
+const char* rtb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB200_H */

@@ -1,0 +1,231 @@
+"""ctypes binding of librtb200.so -- the Python mirror of the reference's entry points.
+
+Names follow the reference: `import_obj` (src/main.rs:114), `create_ground` (src/main.rs:102), `Scene`
+(src/tracer/utils/scene.rs:6), `render` (src/main.rs:242), `render_pixel` (src/main.rs:180).  Everything that
+computes goes through the C ABI of include/rtb200.h into the CUDA library; there is no Python or CPU
+fallback -- if the library is missing or no CUDA device is usable, calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librtb200.so")
+
+RTB_FLAG_COUNTERS = 1
+
+
+class RtbError(RuntimeError):
+    pass
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("n_tris", C.c_uint32), ("verts", C.c_void_p), ("colors", C.c_void_p), ("tie_rank", C.c_void_p),
+                ("light", C.c_float * 9), ("device", C.c_int32)]
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("nb_ray", C.c_uint32), ("nb_light_sample", C.c_uint32),
+                ("eye", C.c_float * 3), ("look_at", C.c_float * 3), ("up", C.c_float * 3), ("distance", C.c_float),
+                ("band_rows", C.c_uint32), ("rank", C.c_uint32), ("world", C.c_uint32), ("flags", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("primary_rays", C.c_uint64), ("primary_hits", C.c_uint64), ("shadow_rays", C.c_uint64),
+                ("shadow_occluded", C.c_uint64), ("box_tests", C.c_uint64), ("tri_tests", C.c_uint64),
+                ("kernel_ms", C.c_float), ("launches", C.c_uint32)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class SceneInfo(C.Structure):
+    _fields_ = [("n_tris", C.c_uint32), ("n_nodes", C.c_uint32), ("max_depth", C.c_uint32), ("ploc_iterations", C.c_uint32),
+                ("sah_cost", C.c_float), ("build_ms", C.c_float)]
+
+
+EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_render",
+           "rtb_render_device", "rtb_render_pixels", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_import_obj",
+           "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
+
+_lib = None
+
+
+def lib():
+    """Loads the CUDA library; fails loudly when it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RtbError("librtb200.so is not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "or `make -C ray-tracer-rust_b200`")
+        L = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        L.rtb_scene_create.argtypes = [vp, vp]
+        L.rtb_scene_destroy.argtypes = [vp]; L.rtb_scene_destroy.restype = None
+        L.rtb_scene_get_info.argtypes = [vp, vp]
+        L.rtb_scene_set_samples.argtypes = [vp, vp, C.c_uint32]
+        L.rtb_render.argtypes = [vp, vp, vp, vp]
+        L.rtb_render_device.argtypes = [vp, vp, vp, vp]
+        L.rtb_render_pixels.argtypes = [vp, vp, vp, C.c_uint64, vp, vp, vp, vp, vp, vp]
+        L.rtb_owned_rows.argtypes = [C.c_uint32] * 4; L.rtb_owned_rows.restype = C.c_uint32
+        L.rtb_deinterleave_bands.argtypes = [C.c_int32, vp, C.c_uint64, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]
+        L.rtb_import_obj.argtypes = [C.c_char_p, vp, vp]
+        L.rtb_free.argtypes = [vp]; L.rtb_free.restype = None
+        L.rtb_fill_samples.argtypes = [C.c_uint64, C.c_uint32, vp]; L.rtb_fill_samples.restype = None
+        L.rtb_write_png.argtypes = [C.c_char_p, vp, C.c_uint32, C.c_uint32]
+        L.rtb_last_error.restype = C.c_char_p
+        L.rtb_version.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise RtbError("rtb200 error %d: %s" % (rc, lib().rtb_last_error().decode("utf-8", "replace")))
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+# ---- host-side entry points kept from main.rs -------------------------------------------------
+
+def import_obj(path):
+    """import_obj (src/main.rs:114-149) -> (n,9) float32.  Like the reference, an unreadable path prints
+    'Not a valid path: ...' and yields no triangles."""
+    verts = C.c_void_p()
+    n = C.c_uint32(0)
+    rc = lib().rtb_import_obj(os.fsencode(path), C.byref(verts), C.byref(n))
+    if rc == -4 and n.value == 0 and lib().rtb_last_error().startswith(b"Not a valid path"):
+        print(lib().rtb_last_error().decode())
+        return np.zeros((0, 9), np.float32)
+    _check(rc)
+    if n.value == 0:
+        return np.zeros((0, 9), np.float32)
+    out = np.ctypeslib.as_array(C.cast(verts, C.POINTER(C.c_float)), shape=(n.value, 9)).copy()
+    lib().rtb_free(verts)
+    return out
+
+
+def create_ground():
+    """create_ground (src/main.rs:102-111): one grey triangle."""
+    return (np.array([[-10000.0, 0.0, -10000.0, 10000.0, 0.0, -10000.0, 0.0, 0.0, 10000.0]], np.float32),
+            np.array([[0.5, 0.5, 0.5]], np.float32))
+
+
+DEFAULT_LIGHT = np.array([-10.0, 300.0, -10.0, 10.0, 300.0, -10.0, 0.0, 300.0, 0.0], np.float32)   # src/main.rs:337-347
+DEFAULT_CAMERA = dict(eye=(0.0, 100.0, 200.0), look_at=(0.0, 0.0, -100000.0), up=(0.0, 1.0, 0.0), distance=288.0)  # :353-356
+
+
+def fill_samples(n_pairs=2000000, seed=0x5EED0001):
+    out = np.empty((n_pairs, 2), np.float32)
+    lib().rtb_fill_samples(C.c_uint64(seed), n_pairs, _ptr(out))
+    return out
+
+
+def write_png(path, rgb8):
+    rgb8 = np.ascontiguousarray(rgb8, np.uint8)
+    h, w, _ = rgb8.shape
+    _check(lib().rtb_write_png(os.fsencode(path), _ptr(rgb8), w, h))
+
+
+def owned_rows(height, band_rows, rank, world):
+    return int(lib().rtb_owned_rows(height, band_rows, rank, world))
+
+
+def owned_row_indices(height, band_rows, rank, world):
+    """Global row numbers, in storage order, of the rows (rank, world) owns."""
+    if world <= 1:
+        return np.arange(height)
+    rows = [np.arange(b * band_rows, min(height, (b + 1) * band_rows))
+            for b in range(rank, (height + band_rows - 1) // band_rows, world)]
+    return np.concatenate(rows) if rows else np.zeros(0, np.int64)
+
+
+# ---- the scene handle ---------------------------------------------------------------------------
+
+class Scene:
+    """Device-resident Scene{light, camera, bvh} (src/tracer/utils/scene.rs:6-12).  Primitives are given in the
+    reference's order: OBJ triangles in argv order, ground last (src/main.rs:324-335)."""
+
+    def __init__(self, verts, colors, light=DEFAULT_LIGHT, device=0, tie_rank=None):
+        self.verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
+        self.colors = np.ascontiguousarray(colors, np.float32).reshape(-1, 3)
+        if self.verts.shape[0] != self.colors.shape[0]:
+            raise ValueError("verts/colors length mismatch")
+        d = SceneDesc()
+        d.n_tris = self.verts.shape[0]
+        d.verts = self.verts.ctypes.data if d.n_tris else None
+        d.colors = self.colors.ctypes.data if d.n_tris else None
+        self._rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, np.int32)
+        d.tie_rank = self._rank.ctypes.data if self._rank is not None else None
+        d.light[:] = [float(x) for x in np.asarray(light, np.float32).reshape(9)]
+        d.device = device
+        self.device = device
+        h = C.c_void_p()
+        _check(lib().rtb_scene_create(C.byref(d), C.byref(h)))
+        self._h = h
+        self._samples = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().rtb_scene_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def info(self):
+        i = SceneInfo()
+        _check(lib().rtb_scene_get_info(self._h, C.byref(i)))
+        return {k: getattr(i, k) for k, _ in SceneInfo._fields_}
+
+    def set_samples(self, samples):
+        s = np.ascontiguousarray(samples, np.float32).reshape(-1, 2)
+        _check(lib().rtb_scene_set_samples(self._h, _ptr(s), s.shape[0]))
+        self._samples = s
+
+    @staticmethod
+    def params(width=1920, height=1080, nb_ray=1, nb_light_sample=100, eye=DEFAULT_CAMERA["eye"],
+               look_at=DEFAULT_CAMERA["look_at"], up=DEFAULT_CAMERA["up"], distance=DEFAULT_CAMERA["distance"],
+               band_rows=8, rank=0, world=1, counters=False):
+        p = RenderParams()
+        p.width, p.height, p.nb_ray, p.nb_light_sample = width, height, nb_ray, nb_light_sample
+        p.eye[:] = [float(x) for x in eye]; p.look_at[:] = [float(x) for x in look_at]; p.up[:] = [float(x) for x in up]
+        p.distance = float(distance)
+        p.band_rows, p.rank, p.world = band_rows, rank, world
+        p.flags = RTB_FLAG_COUNTERS if counters else 0
+        return p
+
+    def render(self, out=None, **kw):
+        """render(scene) (src/main.rs:242-310) minus the PNG save -> ((owned_rows, width, 3) uint8, stats)."""
+        p = self.params(**kw)
+        rows = owned_rows(p.height, p.band_rows, p.rank, max(1, p.world))
+        if out is None:
+            out = np.empty((rows, p.width, 3), np.uint8)
+        st = Stats()
+        _check(lib().rtb_render(self._h, C.byref(p), _ptr(out), C.byref(st)))
+        return out, st.as_dict()
+
+    def render_device(self, d_ptr, stream=0, **kw):
+        """Asynchronous render into device memory (d_ptr: int device address, stream: cudaStream_t as int)."""
+        p = self.params(**kw)
+        _check(lib().rtb_render_device(self._h, C.byref(p), C.c_void_p(d_ptr), C.c_void_p(stream)))
+
+    def render_pixels(self, pixels, **kw):
+        """render_pixel (src/main.rs:180-240) for a list of (px,py) -> dict of per-pixel arrays + stats."""
+        p = self.params(**kw)
+        pixels = np.ascontiguousarray(pixels, np.uint32).reshape(-1, 2)
+        m = pixels.shape[0]
+        out = dict(rgb_lin=np.zeros((m, 3), np.float32), rgb8=np.zeros((m, 3), np.uint8), hit_count=np.zeros(m, np.uint8),
+                   prim0=np.zeros(m, np.int32), t0=np.zeros(m, np.float32))
+        st = Stats()
+        _check(lib().rtb_render_pixels(self._h, C.byref(p), _ptr(pixels), m, _ptr(out["rgb_lin"]), _ptr(out["rgb8"]),
+                                       _ptr(out["hit_count"]), _ptr(out["prim0"]), _ptr(out["t0"]), C.byref(st)))
+        out["stats"] = st.as_dict()
+        return out
+
+
+def deinterleave_bands(device, d_staged, stride_bytes, d_frame, width, height, band_rows, world, stream=0):
+    _check(lib().rtb_deinterleave_bands(device, C.c_void_p(d_staged), stride_bytes, C.c_void_p(d_frame), width, height,
+                                        band_rows, world, C.c_void_p(stream)))

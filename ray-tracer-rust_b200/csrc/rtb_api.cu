@@ -1,0 +1,318 @@
+// rtb_api.cu -- the extern "C" boundary declared in include/rtb200.h.
+// Device scene ownership, per-frame argument marshalling, launches, host<->device copies.
+// There is deliberately no CPU implementation behind any compute entry point.
+#include "rtb_common.cuh"
+#include "../../include/rtb200.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+// launchers / builders defined in the other translation units
+struct RtbBuildInfo { uint32_t n_nodes, max_depth, iterations; float sah_cost, build_ms; };
+cudaError_t rtb_build_scene(const float*, const float*, const int*, uint32_t, float4*, float4*, float4**, int32_t*, RtbBuildInfo*, cudaStream_t);
+cudaError_t rtb_tie_rank_device(const float4* d_tris, uint32_t n, int* d_rank_out, float4* d_colors4, cudaStream_t st);
+cudaError_t rtb_launch_trace_frame(const TraceArgs&, bool, cudaStream_t);
+cudaError_t rtb_launch_trace_list(const TraceArgs&, bool, cudaStream_t);
+cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, cudaStream_t);
+cudaError_t rtb_launch_deinterleave(const uint8_t*, uint64_t, uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, cudaStream_t);
+cudaError_t rtb_upload_gamma_table(const float*);
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+    return code;
+}
+#define CUDA_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail(RTB_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e_)); } while (0)
+
+struct rtb_scene {
+    int device;
+    uint32_t n_tris;
+    float light[9];
+    float4 *d_tris, *d_colors4, *d_nodes;
+    int32_t root;
+    RtbBuildInfo info;
+    float2* d_samples; uint32_t n_samples;
+    float4* d_light_pts; uint32_t light_pts_cap;
+    unsigned long long* d_counters;
+    uint8_t* d_frame; size_t frame_cap;          // staging for rtb_render (host output)
+    uint8_t* h_pinned; size_t pinned_cap;
+    cudaStream_t stream;
+    cudaEvent_t ev0, ev1;
+};
+
+// ---- Color::to_rgba threshold table (color.rs:10-33) ---------------------------------------
+static uint8_t host_gamma_u8(float linear) {
+    const float GAMMA = 2.2f;
+    float g = powf(linear, 1.0f / GAMMA) * 255.0f;
+    if (!(g == g) || g <= 0.0f) return 0;
+    if (g >= 255.0f) return 255;
+    return (uint8_t)g;
+}
+// thr[k] = smallest non-negative f32 whose byte is >= k.  Positive floats order like their bit
+// patterns, so this is a binary search over bit patterns; it assumes libm's powf is monotone,
+// which tests/test_oracle.py and the GPU parity tests check around every threshold.
+static void build_gamma_table(float* thr) {
+    thr[0] = 0.0f;
+    for (int k = 1; k < 256; ++k) {
+        uint32_t lo = 0, hi = 0x40000000u;   // 0.0 .. 2.0
+        while (lo < hi) {
+            uint32_t mid = lo + (hi - lo) / 2;
+            float c; memcpy(&c, &mid, 4);
+            if (host_gamma_u8(c) >= k) hi = mid; else lo = mid + 1;
+        }
+        memcpy(&thr[k], &lo, 4);
+    }
+}
+
+// ---- Camera::new (camera.rs:17-35), unfused f32 on the host ---------------------------------
+static CameraBasis make_camera(const rtb_render_params* p) {
+    CameraBasis c;
+    const f3 eye = mk3(p->eye[0], p->eye[1], p->eye[2]), look = mk3(p->look_at[0], p->look_at[1], p->look_at[2]);
+    c.w = normalize3(sub3(eye, look));
+    const f3 o = normalize3(mk3(p->up[0], p->up[1], p->up[2]));
+    c.u = normalize3(cross3(o, c.w));
+    c.v = normalize3(cross3(c.u, c.w));
+    c.eye = eye;
+    c.distance = p->distance;
+    return c;
+}
+
+extern "C" {
+
+void rtb_set_error_(const char* msg) { snprintf(g_err, sizeof(g_err), "%s", msg ? msg : ""); }
+const char* rtb_last_error(void) { return g_err; }
+const char* rtb_version(void) { return "rtb200 0.1 (sm_100a)"; }
+
+uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint32_t world) {
+    if (world <= 1) return height;
+    if (band_rows == 0 || rank >= world) return 0;
+    const uint32_t n_bands = (height + band_rows - 1) / band_rows;
+    uint32_t rows = 0;
+    for (uint32_t b = rank; b < n_bands; b += world) {
+        const uint32_t y0 = b * band_rows;
+        rows += (height - y0 < band_rows) ? height - y0 : band_rows;
+    }
+    return rows;
+}
+
+void rtb_scene_destroy(rtb_scene* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts);
+    cudaFree(s->d_counters); cudaFree(s->d_frame);
+    if (s->h_pinned) cudaFreeHost(s->h_pinned);
+    if (s->ev0) cudaEventDestroy(s->ev0);
+    if (s->ev1) cudaEventDestroy(s->ev1);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
+    if (!desc || !out) return fail(RTB_ERR_ARG, "rtb_scene_create: null argument");
+    *out = nullptr;
+    if (desc->n_tris && (!desc->verts || !desc->colors)) return fail(RTB_ERR_ARG, "rtb_scene_create: null vertex/colour array");
+    if (desc->n_tris > 0x3fffffffu) return fail(RTB_ERR_LIMIT, "rtb_scene_create: too many primitives");
+    int n_dev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n_dev));
+    if (desc->device < 0 || desc->device >= n_dev) return fail(RTB_ERR_ARG, "rtb_scene_create: device %d of %d", desc->device, n_dev);
+    CUDA_TRY(cudaSetDevice(desc->device));
+
+    float thr[256];
+    build_gamma_table(thr);
+    CUDA_TRY(rtb_upload_gamma_table(thr));
+
+    rtb_scene* s = new rtb_scene();
+    memset(s, 0, sizeof(*s));
+    s->device = desc->device; s->n_tris = desc->n_tris; s->root = RTB_CHILD_NONE;
+    memcpy(s->light, desc->light, sizeof(s->light));
+    const uint32_t n = desc->n_tris;
+    float *d_verts = nullptr, *d_colors = nullptr; int* d_rank = nullptr;
+    int rc = RTB_OK;
+    cudaError_t e;
+#define TRY_(x) do { e = (x); if (e != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e)); goto cleanup; } } while (0)
+    TRY_(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    TRY_(cudaEventCreate(&s->ev0)); TRY_(cudaEventCreate(&s->ev1));
+    TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
+    if (n) {
+        TRY_(cudaMalloc(&d_verts, (size_t)n * 9 * 4)); TRY_(cudaMalloc(&d_colors, (size_t)n * 3 * 4));
+        TRY_(cudaMemcpyAsync(d_verts, desc->verts, (size_t)n * 9 * 4, cudaMemcpyHostToDevice, s->stream));
+        TRY_(cudaMemcpyAsync(d_colors, desc->colors, (size_t)n * 3 * 4, cudaMemcpyHostToDevice, s->stream));
+        if (desc->tie_rank) {
+            TRY_(cudaMalloc(&d_rank, (size_t)n * 4));
+            TRY_(cudaMemcpyAsync(d_rank, desc->tie_rank, (size_t)n * 4, cudaMemcpyHostToDevice, s->stream));
+        }
+        TRY_(cudaMalloc(&s->d_tris, (size_t)n * 3 * sizeof(float4)));
+        TRY_(cudaMalloc(&s->d_colors4, (size_t)n * sizeof(float4)));
+        TRY_(rtb_build_scene(d_verts, d_colors, d_rank, n, s->d_tris, s->d_colors4, &s->d_nodes, &s->root, &s->info, s->stream));
+        if (!desc->tie_rank && n > 1 && n <= RTB_TIE_RANK_MAX_TRIS) {
+            TRY_(rtb_tie_rank_device(s->d_tris, n, nullptr, s->d_colors4, s->stream));
+        }
+        TRY_(cudaStreamSynchronize(s->stream));
+        if (s->info.max_depth > RTB_STACK_SIZE - 1) {
+            rc = fail(RTB_ERR_LIMIT, "BVH depth %u exceeds traversal stack %d", s->info.max_depth, RTB_STACK_SIZE);
+            goto cleanup;
+        }
+    }
+cleanup:
+    cudaFree(d_verts); cudaFree(d_colors); cudaFree(d_rank);
+    if (rc != RTB_OK) { rtb_scene_destroy(s); return rc; }
+    *out = s;
+    return RTB_OK;
+#undef TRY_
+}
+
+int rtb_scene_get_info(const rtb_scene* s, rtb_scene_info* info) {
+    if (!s || !info) return fail(RTB_ERR_ARG, "rtb_scene_get_info: null argument");
+    info->n_tris = s->n_tris; info->n_nodes = s->info.n_nodes; info->max_depth = s->info.max_depth;
+    info->ploc_iterations = s->info.iterations; info->sah_cost = s->info.sah_cost; info->build_ms = s->info.build_ms;
+    return RTB_OK;
+}
+
+int rtb_scene_set_samples(rtb_scene* s, const float* samples, uint32_t n_pairs) {
+    if (!s || !samples || n_pairs == 0) return fail(RTB_ERR_ARG, "rtb_scene_set_samples: null/empty table");
+    CUDA_TRY(cudaSetDevice(s->device));
+    if (n_pairs != s->n_samples) {
+        cudaFree(s->d_samples); s->d_samples = nullptr; s->n_samples = 0;
+        CUDA_TRY(cudaMalloc(&s->d_samples, (size_t)n_pairs * sizeof(float2)));
+        s->n_samples = n_pairs;
+    }
+    CUDA_TRY(cudaMemcpyAsync(s->d_samples, samples, (size_t)n_pairs * sizeof(float2), cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return RTB_OK;
+}
+
+}  // extern "C"
+
+// Validates params, (re)builds the light-point table on `st`, fills TraceArgs.
+static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t st, TraceArgs* a) {
+    if (!s || !p) return fail(RTB_ERR_ARG, "render: null argument");
+    if (!s->d_samples) return fail(RTB_ERR_STATE, "render: rtb_scene_set_samples has not been called");
+    if (p->width == 0 || p->height == 0) return fail(RTB_ERR_ARG, "render: empty frame");
+    const uint32_t world = p->world ? p->world : 1;
+    if (world > 1 && (p->band_rows == 0 || p->rank >= world)) return fail(RTB_ERR_ARG, "render: bad band ownership");
+    CUDA_TRY(cudaSetDevice(s->device));
+    // light points used by a frame: indices (r*nb_ray + i) % n_samples, r < nb_ray, i < nb_light_sample
+    uint64_t need = p->nb_ray ? (uint64_t)(p->nb_ray - 1) * p->nb_ray + p->nb_light_sample : 0;
+    if (need > s->n_samples) need = s->n_samples;
+    if (need > s->light_pts_cap) {
+        cudaFree(s->d_light_pts); s->d_light_pts = nullptr; s->light_pts_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_light_pts, (size_t)need * sizeof(float4)));
+        s->light_pts_cap = (uint32_t)need;
+    }
+    CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, st));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
+    memset(a, 0, sizeof(*a));
+    a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts;
+    a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
+    a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;
+    a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;
+    a->owned_rows = rtb_owned_rows(p->height, a->band_rows, a->rank, world);
+    a->cam = make_camera(p);
+    a->denom = (float)(p->nb_ray * p->nb_light_sample);
+    a->counters = s->d_counters;
+    return RTB_OK;
+}
+
+static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix, float ms, uint32_t launches, rtb_stats* st) {
+    unsigned long long h[RTB_NUM_CTRS];
+    CUDA_TRY(cudaMemcpyAsync(h, s->d_counters, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    if (h[RTB_CTR_OVERFLOW]) return fail(RTB_ERR_LIMIT, "traversal stack overflow");
+    if (st) {
+        st->primary_rays = n_pix * p->nb_ray; st->primary_hits = h[RTB_CTR_PRIMARY_HITS];
+        st->shadow_rays = h[RTB_CTR_SHADOW]; st->shadow_occluded = h[RTB_CTR_OCCLUDED];
+        st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
+        st->kernel_ms = ms; st->launches = launches;
+    }
+    return RTB_OK;
+}
+
+extern "C" {
+
+int rtb_render_device(rtb_scene* s, const rtb_render_params* p, void* d_rgb8, void* cuda_stream) {
+    TraceArgs a;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    int rc = prepare_args(s, p, st, &a);
+    if (rc != RTB_OK) return rc;
+    if (!d_rgb8) return fail(RTB_ERR_ARG, "rtb_render_device: null output");
+    a.rgb8 = (uint8_t*)d_rgb8;
+    CUDA_TRY(rtb_launch_trace_frame(a, (p->flags & RTB_FLAG_COUNTERS) != 0, st));
+    return RTB_OK;
+}
+
+int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stats* stats) {
+    TraceArgs a;
+    if (!rgb8) return fail(RTB_ERR_ARG, "rtb_render: null output");
+    int rc = prepare_args(s, p, s ? s->stream : nullptr, &a);
+    if (rc != RTB_OK) return rc;
+    const size_t bytes = (size_t)a.owned_rows * a.width * 3;
+    if (bytes > s->frame_cap) {
+        cudaFree(s->d_frame); s->d_frame = nullptr; s->frame_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_frame, bytes));
+        s->frame_cap = bytes;
+    }
+    a.rgb8 = s->d_frame;
+    CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
+    CUDA_TRY(rtb_launch_trace_frame(a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream));
+    CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
+    if (bytes) CUDA_TRY(cudaMemcpyAsync(rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 2, stats);
+}
+
+int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* pixels, uint64_t n_pix, float* rgb_lin,
+                      uint8_t* rgb8, uint8_t* hit_count, int32_t* prim0, float* t0, rtb_stats* stats) {
+    TraceArgs a;
+    if (n_pix && !pixels) return fail(RTB_ERR_ARG, "rtb_render_pixels: null pixel list");
+    int rc = prepare_args(s, p, s ? s->stream : nullptr, &a);
+    if (rc != RTB_OK) return rc;
+    uint2* d_pix = nullptr; float* d_lin = nullptr; uint8_t* d_rgb8 = nullptr; uint8_t* d_hc = nullptr; int32_t* d_p0 = nullptr; float* d_t0 = nullptr;
+    cudaError_t e = cudaSuccess;
+    float ms = 0.0f;
+#define TRY_(x) do { e = (x); if (e != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e)); goto cleanup; } } while (0)
+    if (n_pix) {
+        TRY_(cudaMalloc(&d_pix, n_pix * sizeof(uint2)));
+        TRY_(cudaMemcpyAsync(d_pix, pixels, n_pix * sizeof(uint2), cudaMemcpyHostToDevice, s->stream));
+        if (rgb_lin) TRY_(cudaMalloc(&d_lin, n_pix * 12));
+        if (rgb8) TRY_(cudaMalloc(&d_rgb8, n_pix * 3));
+        if (hit_count) TRY_(cudaMalloc(&d_hc, n_pix));
+        if (prim0) TRY_(cudaMalloc(&d_p0, n_pix * 4));
+        if (t0) TRY_(cudaMalloc(&d_t0, n_pix * 4));
+    }
+    a.pixel_list = d_pix; a.n_pix = n_pix; a.out_rgb_lin = d_lin; a.rgb8 = d_rgb8; a.out_hit_count = d_hc; a.out_prim0 = d_p0; a.out_t0 = d_t0;
+    TRY_(cudaEventRecord(s->ev0, s->stream));
+    TRY_(rtb_launch_trace_list(a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream));
+    TRY_(cudaEventRecord(s->ev1, s->stream));
+    if (n_pix) {
+        if (rgb_lin) TRY_(cudaMemcpyAsync(rgb_lin, d_lin, n_pix * 12, cudaMemcpyDeviceToHost, s->stream));
+        if (rgb8) TRY_(cudaMemcpyAsync(rgb8, d_rgb8, n_pix * 3, cudaMemcpyDeviceToHost, s->stream));
+        if (hit_count) TRY_(cudaMemcpyAsync(hit_count, d_hc, n_pix, cudaMemcpyDeviceToHost, s->stream));
+        if (prim0) TRY_(cudaMemcpyAsync(prim0, d_p0, n_pix * 4, cudaMemcpyDeviceToHost, s->stream));
+        if (t0) TRY_(cudaMemcpyAsync(t0, d_t0, n_pix * 4, cudaMemcpyDeviceToHost, s->stream));
+    }
+    TRY_(cudaStreamSynchronize(s->stream));
+    TRY_(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    rc = fetch_stats(s, p, n_pix, ms, 2, stats);
+cleanup:
+    cudaFree(d_pix); cudaFree(d_lin); cudaFree(d_rgb8); cudaFree(d_hc); cudaFree(d_p0); cudaFree(d_t0);
+    return rc;
+#undef TRY_
+}
+
+int rtb_deinterleave_bands(int32_t device, const void* d_staged, uint64_t stride_bytes, void* d_frame, uint32_t width,
+                           uint32_t height, uint32_t band_rows, uint32_t world, void* cuda_stream) {
+    if (!d_staged || !d_frame || band_rows == 0 || world == 0) return fail(RTB_ERR_ARG, "rtb_deinterleave_bands: bad argument");
+    CUDA_TRY(cudaSetDevice(device));
+    CUDA_TRY(rtb_launch_deinterleave((const uint8_t*)d_staged, stride_bytes, (uint8_t*)d_frame, width * 3, height, band_rows, world,
+                                     (cudaStream_t)cuda_stream));
+    return RTB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,66 @@
+// rtb_common.cuh -- shared device/host declarations of the B200 ray-casting path.
+//
+// Arithmetic contract.  The whole library is compiled with -fmad=false (and the default
+// -prec-div=true -prec-sqrt=true -ftz=false), so every `a*b+c`, `/` and sqrtf below is the
+// same correctly-rounded, unfused IEEE binary32 operation the reference's rustc/nalgebra code
+// performs.  The only fused operations are the explicit fmaf() calls of the conservative
+// inner-node slab test (rtb_trace.cu), which never decides a result on its own.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <float.h>
+
+#define RTB_STACK_SIZE 64          // traversal stack entries (binary BVH depth limit)
+#define RTB_CHILD_NONE 0x7fffffff  // absent child (single-primitive scenes)
+
+struct f3 { float x, y, z; };
+
+__host__ __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__host__ __device__ __forceinline__ f3 sub3(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__host__ __device__ __forceinline__ f3 add3(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__host__ __device__ __forceinline__ f3 scale3(float s, f3 a) { return mk3(s * a.x, s * a.y, s * a.z); }
+// nalgebra 0.11 dot: fold from zero, left to right.  The leading "0 +" only affects the sign of
+// an all-zero result, which no consumer on this path can observe, so it is dropped.
+__host__ __device__ __forceinline__ float dot3(f3 a, f3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__host__ __device__ __forceinline__ f3 cross3(f3 a, f3 b) {
+    return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__host__ __device__ __forceinline__ float norm3(f3 a) { return sqrtf(dot3(a, a)); }
+// Unit::new_normalize: component-wise true division by the norm (ray.rs:15, camera.rs:22-32, triangle.rs:29)
+__host__ __device__ __forceinline__ f3 normalize3(f3 a) {
+    float n = norm3(a);
+    return mk3(a.x / n, a.y / n, a.z / n);
+}
+
+// Camera basis (src/tracer/utils/camera.rs:17-35), computed once per frame on the host in the same
+// unfused f32 arithmetic (host compilers are given -ffp-contract=off).
+struct CameraBasis { f3 u, v, w, eye; float distance; };
+
+// Everything a trace kernel needs, passed by value as a kernel parameter.
+struct TraceArgs {
+    const float4* __restrict__ tris;     // 3 float4 per primitive: {v0,n.x} {v1,n.y} {v2,n.z}
+    const float4* __restrict__ colors;   // 1 float4 per primitive: {r,g,b, tie_rank as int bits}
+    const float4* __restrict__ nodes;    // 4 float4 per inner node (layout in rtb_bvh.cu)
+    const float2* __restrict__ samples;  // n_samples (u,v) pairs
+    const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table
+    uint32_t n_tris, n_samples, n_light_pts;
+    int32_t root;                        // node index, ~prim for a single-primitive scene, RTB_CHILD_NONE if empty
+    uint32_t width, height, nb_ray, nb_light_sample;
+    uint32_t band_rows, rank, world, owned_rows;
+    CameraBasis cam;
+    float denom;                         // (NB_RAY * NB_LIGHT_SAMPLE) as f32 (src/main.rs:211)
+    // outputs
+    uint8_t* rgb8;                       // frame mode: owned rows, compact
+    const uint2* pixel_list;             // list mode
+    uint64_t n_pix;
+    float* out_rgb_lin; uint8_t* out_hit_count; int32_t* out_prim0; float* out_t0;
+    unsigned long long* counters;        // [0] primary hits [1] shadow rays [2] occluded [3] box tests [4] tri tests [5] stack overflow
+};
+
+#define RTB_CTR_PRIMARY_HITS 0
+#define RTB_CTR_SHADOW 1
+#define RTB_CTR_OCCLUDED 2
+#define RTB_CTR_BOX 3
+#define RTB_CTR_TRI 4
+#define RTB_CTR_OVERFLOW 5
+#define RTB_NUM_CTRS 8
