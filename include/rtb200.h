@@ -110,6 +110,14 @@ int rtb_render_pixels(rtb_scene* scene, const rtb_render_params* params, const u
                       float* rgb_lin, uint8_t* rgb8, uint8_t* hit_count, int32_t* prim0, float* t0,
                       rtb_stats* stats);
 
+/* --- replaces Color::to_rgba (src/tracer/utils/color.rs:26-33) on its own: n linear f32 values (HOST) -> n bytes
+ *     (HOST), computed by the same device code the trace kernel's epilogue uses. */
+int rtb_color_to_u8(rtb_scene* scene, const float* linear, uint64_t n, uint8_t* out);
+
+/* The tie ranks in use (HOST array of n_tris int32): the leaf order of the reference's tree as replayed on the
+ * device, or the caller's, or the primitive index (see rtb_scene_desc.tie_rank). */
+int rtb_scene_get_tie_ranks(rtb_scene* scene, int32_t* out);
+
 /* Rows owned by (rank, world) for a frame of `height` rows in bands of band_rows. */
 uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint32_t world);
 

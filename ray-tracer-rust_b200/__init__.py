@@ -2,5 +2,6 @@
 
 The directory name is not a Python identifier; import it through the root-level `rtb200` shim.
 """
+from . import binding  # noqa: F401
 from .binding import *  # noqa: F401,F403
 from .binding import lib, LIB_PATH, EXPORTS, Scene, RtbError  # noqa: F401

@@ -20,6 +20,8 @@ cudaError_t rtb_launch_trace_list(const TraceArgs&, bool, cudaStream_t);
 cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, cudaStream_t);
 cudaError_t rtb_launch_deinterleave(const uint8_t*, uint64_t, uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, cudaStream_t);
 cudaError_t rtb_upload_gamma_table(const float*);
+cudaError_t rtb_launch_color_to_u8(const float*, uint64_t, uint8_t*, cudaStream_t);
+cudaError_t rtb_launch_get_ranks(const float4*, uint32_t, int*, cudaStream_t);
 
 static thread_local char g_err[512] = "";
 
@@ -55,7 +57,7 @@ static uint8_t host_gamma_u8(float linear) {
 }
 // thr[k] = smallest non-negative f32 whose byte is >= k.  Positive floats order like their bit
 // patterns, so this is a binary search over bit patterns; it assumes libm's powf is monotone,
-// which tests/test_oracle.py and the GPU parity tests check around every threshold.
+// which the CPU and GPU test suites check around every threshold.
 static void build_gamma_table(float* thr) {
     thr[0] = 0.0f;
     for (int k = 1; k < 256; ++k) {
@@ -304,6 +306,38 @@ cleanup:
     cudaFree(d_pix); cudaFree(d_lin); cudaFree(d_rgb8); cudaFree(d_hc); cudaFree(d_p0); cudaFree(d_t0);
     return rc;
 #undef TRY_
+}
+
+int rtb_color_to_u8(rtb_scene* s, const float* linear, uint64_t n, uint8_t* out) {
+    if (!s || (n && (!linear || !out))) return fail(RTB_ERR_ARG, "rtb_color_to_u8: null argument");
+    if (n == 0) return RTB_OK;
+    CUDA_TRY(cudaSetDevice(s->device));
+    float* d_in = nullptr; uint8_t* d_out = nullptr;
+    int rc = RTB_OK; cudaError_t e;
+#define TRY_(x) do { e = (x); if (e != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e)); goto cleanup; } } while (0)
+    TRY_(cudaMalloc(&d_in, n * 4)); TRY_(cudaMalloc(&d_out, n));
+    TRY_(cudaMemcpyAsync(d_in, linear, n * 4, cudaMemcpyHostToDevice, s->stream));
+    TRY_(rtb_launch_color_to_u8(d_in, n, d_out, s->stream));
+    TRY_(cudaMemcpyAsync(out, d_out, n, cudaMemcpyDeviceToHost, s->stream));
+    TRY_(cudaStreamSynchronize(s->stream));
+cleanup:
+    cudaFree(d_in); cudaFree(d_out);
+    return rc;
+#undef TRY_
+}
+
+int rtb_scene_get_tie_ranks(rtb_scene* s, int32_t* out) {
+    if (!s || !out) return fail(RTB_ERR_ARG, "rtb_scene_get_tie_ranks: null argument");
+    if (s->n_tris == 0) return RTB_OK;
+    CUDA_TRY(cudaSetDevice(s->device));
+    int* d = nullptr;
+    CUDA_TRY(cudaMalloc(&d, (size_t)s->n_tris * 4));
+    cudaError_t e = rtb_launch_get_ranks(s->d_colors4, s->n_tris, d, s->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d, (size_t)s->n_tris * 4, cudaMemcpyDeviceToHost, s->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(RTB_ERR_CUDA, "rtb_scene_get_tie_ranks: %s", cudaGetErrorString(e));
+    return RTB_OK;
 }
 
 int rtb_deinterleave_bands(int32_t device, const void* d_staged, uint64_t stride_bytes, void* d_frame, uint32_t width,

@@ -1,0 +1,79 @@
+"""Multi-GPU frame assembly: one process per GPU, scene replicated, interleaved row bands, one gather to rank 0.
+
+Replaces the thread fan-out of render() (src/main.rs:269-303): where the reference gives each CPU thread a slice
+of a shuffled pixel list and serialises put_pixel behind a Mutex, here rank r renders every band b with
+b % world == r straight into its NCCL send buffer (rtb_render_device), the buffers are gathered to rank 0 over
+NVLink, and rank 0 runs the de-interleave kernel (rtb_deinterleave_bands).  Pixels are independent, so there is no
+other exchange.  torch / torch.distributed are used for device memory, streams and the collective only.
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import binding
+
+
+def padded_stride(width, height, band_rows, world):
+    """Bytes per rank in the gather: the largest band set, rounded up to 16 B (uint4 copies, equal-size gather)."""
+    rows = max(binding.owned_rows(height, band_rows, r, world) for r in range(world))
+    return (rows * width * 3 + 15) // 16 * 16
+
+
+class BandGather:
+    """Owns the send buffer (all ranks), the staging buffer and the final frame (rank 0)."""
+
+    def __init__(self, width, height, band_rows, rank, world, device, group=None):
+        self.width, self.height, self.band_rows, self.rank, self.world = width, height, band_rows, rank, world
+        self.device = torch.device(device)
+        self.group = group
+        self.stride = padded_stride(width, height, band_rows, world)
+        self.rows = binding.owned_rows(height, band_rows, rank, world)
+        self.send = torch.zeros(self.stride, dtype=torch.uint8, device=self.device)
+        self.staged = None
+        self.frame = None
+        if rank == 0:
+            self.staged = torch.zeros(world * self.stride, dtype=torch.uint8, device=self.device)
+            self.frame = torch.zeros(height * width * 3, dtype=torch.uint8, device=self.device)
+
+    def collect(self):
+        """The collective alone: per-rank compact buffers -> rank 0's staging buffer (world x stride)."""
+        if self.rank == 0:
+            parts = list(self.staged.view(self.world, self.stride).unbind(0))
+            dist.gather(self.send, parts, dst=0, group=self.group)
+        else:
+            dist.gather(self.send, None, dst=0, group=self.group)
+
+    def gather(self):
+        """Collective + placement: after it returns (stream-ordered) rank 0's self.frame holds the row-major RGB8
+        frame.  world == 1 needs neither: the send buffer already is the frame."""
+        if self.world == 1:
+            self.frame = self.send[: self.height * self.width * 3]
+            return self.frame
+        self.collect()
+        if self.rank != 0:
+            return None
+        if not self.staged.is_cuda:
+            raise binding.RtbError("de-interleave runs on the GPU only (no CPU path)")
+        binding.deinterleave_bands(self.device.index or 0, self.staged.data_ptr(), self.stride, self.frame.data_ptr(),
+                                   self.width, self.height, self.band_rows, self.world,
+                                   torch.cuda.current_stream(self.device).cuda_stream)
+        return self.frame
+
+
+def render_distributed(scene, gather, **params):
+    """One frame on this rank's bands + the gather.  Asynchronous on the current torch stream of the scene's device."""
+    stream = torch.cuda.current_stream(gather.device).cuda_stream
+    scene.render_device(gather.send.data_ptr(), stream, width=gather.width, height=gather.height,
+                        band_rows=gather.band_rows, rank=gather.rank, world=gather.world, **params)
+    return gather.gather()
+
+
+def assemble_on_host(per_rank_rows, width, height, band_rows, world):
+    """Bookkeeping mirror of the de-interleave for host-side tests: list of per-rank compact byte buffers (possibly
+    padded) -> (height, width, 3) frame."""
+    frame = np.zeros((height, width, 3), np.uint8)
+    for r in range(world):
+        idx = binding.owned_row_indices(height, band_rows, r, world)
+        buf = np.asarray(per_rank_rows[r], np.uint8).ravel()[: len(idx) * width * 3]
+        frame[idx] = buf.reshape(len(idx), width, 3)
+    return frame

@@ -1,0 +1,96 @@
+// rt_main.cpp -- host driver with the reference's command line: every plain argument is an OBJ path
+// (src/main.rs:321,328-331); the scene is OBJ triangles + ground + light + camera exactly as main()
+// builds it (src/main.rs:319-358); output.png is written in the current directory
+// (src/main.rs:312-315).  The render itself is the C ABI call into the CUDA library.  Optional
+// --flags expose the reference's compile-time constants; their defaults are the reference's values.
+#include "../../include/rtb200.h"
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+int main(int argc, char** argv) {
+    uint32_t width = 1920, height = 1080;        // src/main.rs:350-351
+    uint32_t nb_ray = 1, nb_light = 100;         // src/main.rs:38-39
+    uint32_t n_samples = 2000000;                // src/main.rs:40
+    float distance = 288.0f;                     // src/main.rs:356
+    uint64_t seed = 0x5EED0001ull;
+    int device = 0;
+    std::string out = "output.png";
+    std::vector<std::string> objs;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        auto need = [&](const char* name) -> const char* {
+            if (i + 1 >= argc) { fprintf(stderr, "%s needs a value\n", name); exit(2); }
+            return argv[++i];
+        };
+        if (a == "--width") width = (uint32_t)atoi(need("--width"));
+        else if (a == "--height") height = (uint32_t)atoi(need("--height"));
+        else if (a == "--spp") nb_ray = (uint32_t)atoi(need("--spp"));
+        else if (a == "--light-samples") nb_light = (uint32_t)atoi(need("--light-samples"));
+        else if (a == "--distance") distance = (float)atof(need("--distance"));
+        else if (a == "--seed") seed = strtoull(need("--seed"), nullptr, 0);
+        else if (a == "--device") device = atoi(need("--device"));
+        else if (a == "--out") out = need("--out");
+        else objs.push_back(a);
+    }
+
+    printf("Building scene\n");                  // src/main.rs:322
+    std::vector<float> verts, colors;
+    for (const std::string& path : objs) {
+        float* v = nullptr; uint32_t n = 0;
+        int rc = rtb_import_obj(path.c_str(), &v, &n);
+        if (rc != RTB_OK) {
+            if (n == 0 && strncmp(rtb_last_error(), "Not a valid path", 16) == 0) { printf("%s\n", rtb_last_error()); continue; }
+            fprintf(stderr, "%s\n", rtb_last_error());
+            return 1;
+        }
+        verts.insert(verts.end(), v, v + (size_t)n * 9);
+        for (uint32_t k = 0; k < n; ++k) { colors.push_back(1.0f); colors.push_back(1.0f); colors.push_back(1.0f); }   // :143
+        rtb_free(v);
+    }
+    const float ground[9] = {-10000.0f, 0.0f, -10000.0f, 10000.0f, 0.0f, -10000.0f, 0.0f, 0.0f, 10000.0f};   // :102-111
+    verts.insert(verts.end(), ground, ground + 9);
+    colors.push_back(0.5f); colors.push_back(0.5f); colors.push_back(0.5f);
+
+    rtb_scene_desc desc;
+    memset(&desc, 0, sizeof(desc));
+    desc.n_tris = (uint32_t)(verts.size() / 9);
+    desc.verts = verts.data(); desc.colors = colors.data(); desc.tie_rank = nullptr; desc.device = device;
+    const float light[9] = {-10.0f, 300.0f, -10.0f, 10.0f, 300.0f, -10.0f, 0.0f, 300.0f, 0.0f};             // :337-343
+    memcpy(desc.light, light, sizeof(light));
+    rtb_scene* scene = nullptr;
+    if (rtb_scene_create(&desc, &scene) != RTB_OK) { fprintf(stderr, "%s\n", rtb_last_error()); return 1; }
+
+    std::vector<float> samples((size_t)n_samples * 2);
+    rtb_fill_samples(seed, n_samples, samples.data());
+    if (rtb_scene_set_samples(scene, samples.data(), n_samples) != RTB_OK) { fprintf(stderr, "%s\n", rtb_last_error()); return 1; }
+
+    rtb_render_params prm;
+    memset(&prm, 0, sizeof(prm));
+    prm.width = width; prm.height = height; prm.nb_ray = nb_ray; prm.nb_light_sample = nb_light;
+    prm.eye[0] = 0.0f; prm.eye[1] = 100.0f; prm.eye[2] = 200.0f;                                             // :353
+    prm.look_at[0] = 0.0f; prm.look_at[1] = 0.0f; prm.look_at[2] = -100000.0f;                               // :354
+    prm.up[0] = 0.0f; prm.up[1] = 1.0f; prm.up[2] = 0.0f;                                                    // :355
+    prm.distance = distance;
+    prm.world = 1;
+
+    printf("Rendering...\n");                    // src/main.rs:360
+    std::vector<uint8_t> img((size_t)width * height * 3);
+    rtb_stats st;
+    auto t0 = std::chrono::steady_clock::now();
+    if (rtb_render(scene, &prm, img.data(), &st) != RTB_OK) { fprintf(stderr, "%s\n", rtb_last_error()); return 1; }
+    double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    // src/main.rs:305-310 prints whole seconds and primary rays only; sub-second frames need decimals
+    printf("Rendered in %.6f seconds (kernel %.3f ms)\n", secs, st.kernel_ms);
+    printf("Throughput %.1fM ray/s primary, %.1fM ray/s primary+shadow\n", (double)st.primary_rays / 1e6 / secs,
+           (double)(st.primary_rays + st.shadow_rays) / 1e6 / secs);
+
+    printf("Writting image to disk\n");          // src/main.rs:312 [sic]
+    if (rtb_write_png(out.c_str(), img.data(), width, height) != RTB_OK) { fprintf(stderr, "%s\n", rtb_last_error()); return 1; }
+    rtb_scene_destroy(scene);
+    return 0;
+}

@@ -1,0 +1,254 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on the same seeded
+inputs.  Bars: hit masks, hit primitive, hit distance bits, linear colour bits and RGB8 bytes all EXACT (the
+north_star allows +-1 LSB on 0.1 % of channels and grazing-ray mask differences; this design needs neither)."""
+import numpy as np
+import pytest
+
+import scenes as S
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+CAM = dict(eye=S.EYE, look_at=S.LOOK_AT, up=S.UP)
+
+
+@pytest.fixture(scope="module")
+def rtb(built):
+    import rtb200
+    return rtb200
+
+
+@pytest.fixture(scope="module")
+def gpu_big_bunny(rtb, big_bunny_inputs):
+    v, c, smp = big_bunny_inputs
+    sc = rtb.Scene(v, c)
+    sc.set_samples(smp)
+    return sc
+
+
+def assert_same(g, o, what=""):
+    assert (g["hit_count"] == o["hit_count"]).all(), what + " hit mask"
+    assert (g["prim0"] == o["prim0"]).all(), what + " hit primitive"
+    assert (g["t0"].view(np.uint32) == o["t0"].view(np.uint32)).all(), what + " hit distance bits"
+    assert (g["rgb_lin"].view(np.uint32) == o["rgb_lin"].view(np.uint32)).all(), what + " linear colour bits"
+    assert (g["rgb8"] == o["rgb8"]).all(), what + " rgb8"
+    for k in ("primary_rays", "primary_hits", "shadow_rays", "shadow_occluded"):
+        assert g["stats"][k] == o["stats"][k], what + " " + k
+
+
+def test_scene_info(gpu_big_bunny):
+    info = gpu_big_bunny.info()
+    assert info["n_tris"] == 4969 and info["n_nodes"] == 4968
+    assert 10 <= info["max_depth"] < 64
+
+
+def test_big_bunny_1080p_subset_exact(gpu_big_bunny, oracle_big_bunny, big_bunny_inputs):
+    """BASELINE config 2 on a stratified 1/400 pixel subset, reference-tree oracle."""
+    _, _, smp = big_bunny_inputs
+    pix = S.stratified_pixels(S.WIDTH, S.HEIGHT, 20, seed=9)
+    g = gpu_big_bunny.render_pixels(pix, counters=True)
+    o = oracle_big_bunny.render(S.WIDTH, S.HEIGHT, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix)
+    assert_same(g, o, "big_bunny 1080p")
+    assert g["stats"]["box_tests"] > 0 and g["stats"]["tri_tests"] > 0
+    assert g["stats"]["box_tests"] < o["stats"]["box_tests"] / 20     # the point of building our own tree
+
+
+def test_bunny_region_dense_exact(gpu_big_bunny, oracle_big_bunny, big_bunny_inputs):
+    """Every pixel of a window over the bunny's head and its shadow edge (silhouettes, grazing rays)."""
+    _, _, smp = big_bunny_inputs
+    xs, ys = np.meshgrid(np.arange(800, 960, 2), np.arange(440, 520, 2))
+    pix = np.stack([xs.ravel(), ys.ravel()], 1).astype(np.uint32)
+    g = gpu_big_bunny.render_pixels(pix)
+    o = oracle_big_bunny.render(S.WIDTH, S.HEIGHT, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix,
+                                nb_light_sample=100)
+    assert_same(g, o, "bunny window")
+    assert ((g["prim0"] >= 0) & (g["prim0"] < 4968)).mean() > 0.3
+
+
+def test_frame_kernel_equals_list_kernel_and_oracle(gpu_big_bunny, oracle_big_bunny, big_bunny_inputs):
+    _, _, smp = big_bunny_inputs
+    frame, st = gpu_big_bunny.render()
+    assert frame.shape == (S.HEIGHT, S.WIDTH, 3)
+    pix = S.stratified_pixels(S.WIDTH, S.HEIGHT, 24, seed=4)
+    o = oracle_big_bunny.render(S.WIDTH, S.HEIGHT, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix)
+    assert (frame[pix[:, 1], pix[:, 0]] == o["rgb8"]).all()
+    assert st["primary_rays"] == S.WIDTH * S.HEIGHT
+    assert 0.45 < st["primary_hits"] / st["primary_rays"] < 0.55
+    assert st["shadow_rays"] == st["primary_hits"] * 100
+    # sky is black (image zero-initialised, src/main.rs:247), ground is lit
+    assert frame[:400].max() == 0 and frame[900:, :, :].min() > 100
+    # determinism: the reference is not (thread_rng); this path must be
+    frame2, _ = gpu_big_bunny.render()
+    assert (frame == frame2).all()
+
+
+def test_4k_16spp_subset_exact(gpu_big_bunny, oracle_big_bunny, big_bunny_inputs):
+    """BASELINE config 3 (the bench workload) on a pixel subset: 16 rays/pixel, light-sample indices up to 339."""
+    _, _, smp = big_bunny_inputs
+    rng = np.random.default_rng(1)
+    pix = np.stack([rng.integers(0, 3840, 150), rng.integers(900, 2160, 150)], 1).astype(np.uint32)
+    pix = np.concatenate([pix, [[1800 + i, 1000 + j] for i in range(0, 200, 20) for j in range(0, 200, 20)]]).astype(np.uint32)
+    g = gpu_big_bunny.render_pixels(pix, width=3840, height=2160, nb_ray=16)
+    o = oracle_big_bunny.render(3840, 2160, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix, nb_ray=16)
+    assert_same(g, o, "4K 16spp")
+    assert g["hit_count"].max() == 16
+
+
+def test_small_bunny_config1_exact(rtb, built):
+    """BASELINE config 1: bunny.obj is sub-pixel at the default camera and many of its triangles fail the absolute
+    |det| < 1e-5 test."""
+    v, c = S.small_bunny()
+    smp = S.make_samples()
+    sc = rtb.Scene(v, c)
+    sc.set_samples(smp)
+    osc = O.OracleScene(v, c, True)
+    pix = np.concatenate([S.stratified_pixels(S.WIDTH, S.HEIGHT, 40, seed=3),
+                          [[x, y] for x in range(955, 966) for y in range(880, 900)]]).astype(np.uint32)
+    g = sc.render_pixels(pix)
+    o = osc.render(S.WIDTH, S.HEIGHT, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix)
+    assert_same(g, o, "bunny.obj")
+
+
+@pytest.mark.parametrize("seed,n,spp,nls", [(1, 200, 1, 16), (2, 1000, 3, 7), (3, 37, 2, 100), (4, 2, 1, 5)])
+def test_random_soup_full_frames_exact(rtb, built, seed, n, spp, nls):
+    """Coloured triangle soups (interpenetrating, sliver and back-facing triangles), full small frames whose
+    size is not a multiple of the 32x8 block tile."""
+    v, c = S.random_soup(n, seed=seed)
+    smp = S.make_samples(7919, seed=seed)              # short table: exercises the modulo wrap
+    W, H = 150, 83
+    sc = rtb.Scene(v, c)
+    sc.set_samples(smp)
+    osc = O.OracleScene(v, c, True)
+    o = osc.render(W, H, smp, S.EYE, S.LOOK_AT, S.UP, 50.0, S.LIGHT, nb_ray=spp, nb_light_sample=nls)
+    frame, st = sc.render(width=W, height=H, distance=50.0, nb_ray=spp, nb_light_sample=nls)
+    assert (frame == o["rgb8"]).all()
+    ys, xs = np.mgrid[0:H, 0:W]
+    pix = np.stack([xs.ravel(), ys.ravel()], 1).astype(np.uint32)
+    g = sc.render_pixels(pix, width=W, height=H, distance=50.0, nb_ray=spp, nb_light_sample=nls)
+    flat = {k: (o[k].reshape(-1, 3) if o[k].ndim == 3 else o[k].ravel()) for k in ("rgb_lin", "rgb8", "hit_count", "prim0", "t0")}
+    flat["stats"] = o["stats"]
+    assert_same(g, flat, "soup %d" % seed)
+
+
+def test_zero_jitter_axis_aligned_rays(gpu_big_bunny, rtb, oracle_big_bunny, big_bunny_inputs):
+    """All-zero sample table: column px = width/2 has d.x == 0 exactly (inf/NaN slab arithmetic in the reference);
+    those rays take the cull-nothing path here and must still agree."""
+    v, c, _ = big_bunny_inputs
+    zero = np.zeros((1000, 2), np.float32)
+    sc = rtb.Scene(v, c)
+    sc.set_samples(zero)
+    pix = np.array([[960, y] for y in range(0, 1080, 9)] + [[959, 700], [961, 700], [0, 0], [1919, 1079]], np.uint32)
+    g = sc.render_pixels(pix, nb_light_sample=3)
+    o = oracle_big_bunny.render(S.WIDTH, S.HEIGHT, zero, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix, nb_light_sample=3)
+    assert_same(g, o, "zero jitter")
+    assert o["stats"]["nan_asserts"] == 0
+
+
+def test_orbit_poses_exact(gpu_big_bunny, oracle_big_bunny, big_bunny_inputs):
+    """BASELINE config 5 poses (camera-only change, scene stays resident)."""
+    _, _, smp = big_bunny_inputs
+    pix = S.stratified_pixels(S.WIDTH, S.HEIGHT, 60, seed=8)
+    for k in (0, 17, 60, 95):
+        eye, look, up = S.orbit_pose(k)
+        g = gpu_big_bunny.render_pixels(pix, eye=eye, look_at=look, up=up, nb_light_sample=20)
+        o = oracle_big_bunny.render(S.WIDTH, S.HEIGHT, smp, eye, look, up, S.DISTANCE, S.LIGHT, pixels=pix, nb_light_sample=20)
+        assert_same(g, o, "orbit pose %d" % k)
+
+
+def test_instanced_bunnies_subset(rtb, built):
+    """BASELINE config 4 scene (64 copies, 317 953 primitives); oracle in brute-force mode (no reference tree:
+    O(n^2) build), tie rule = primitive index on both sides."""
+    v, c = S.instanced_bunnies(8)
+    assert len(v) == 317953
+    smp = S.make_samples()
+    sc = rtb.Scene(v, c)
+    sc.set_samples(smp)
+    assert (sc.tie_ranks() == np.arange(len(v))).all()
+    rng = np.random.default_rng(5)
+    pix = np.stack([rng.integers(0, 3840, 120), rng.integers(700, 2160, 120)], 1).astype(np.uint32)
+    g = sc.render_pixels(pix, width=3840, height=2160, nb_light_sample=6)
+    o = O.OracleScene(v, c, False).render(3840, 2160, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix,
+                                          nb_light_sample=6, mode=O.MODE_BRUTE)
+    assert_same(g, o, "64 bunnies")
+    assert (g["prim0"] >= 0).sum() > 60
+
+
+def test_tie_ranks_replay_reference_tree(gpu_big_bunny, oracle_big_bunny, rtb, built):
+    assert (gpu_big_bunny.tie_ranks() == oracle_big_bunny.dfs_rank()).all()
+    for seed, n in ((1, 2), (2, 3), (3, 64), (4, 1025), (5, 3000)):
+        v, c = S.random_soup(n, seed=seed, with_ground=(seed % 2 == 0))
+        assert (rtb.Scene(v, c).tie_ranks() == O.OracleScene(v, c, True).dfs_rank()).all(), n
+
+
+def test_exact_distance_ties_follow_reference_leaf_order(rtb, built):
+    """Coincident triangles with different colours: equal t bit for bit, the later leaf of the reference's tree wins
+    (bounding_volume_hierarchy.rs:123-130)."""
+    base = np.array([-40, 20, -60, 40, 20, -60, 0, 90, -60], np.float32)
+    v = np.stack([base, base, base, base + np.float32(500.0)] + [S.GROUND[0]])
+    c = np.array([[1, 0, 0], [0, 1, 0], [0, 0, 1], [1, 1, 1], [0.5, 0.5, 0.5]], np.float32)
+    smp = S.make_samples(5000, seed=3)
+    sc = rtb.Scene(v, c)
+    sc.set_samples(smp)
+    osc = O.OracleScene(v, c, True)
+    W, H = 96, 54
+    o = osc.render(W, H, smp, S.EYE, S.LOOK_AT, S.UP, 30.0, S.LIGHT, nb_light_sample=4)
+    frame, _ = sc.render(width=W, height=H, distance=30.0, nb_light_sample=4)
+    assert (frame == o["rgb8"]).all()
+    hit = (o["prim0"] >= 0) & (o["prim0"] < 3)
+    assert hit.sum() > 20 and len(np.unique(o["prim0"][hit])) == 1      # always the same one of the three
+
+
+def test_edge_cases(rtb, built):
+    smp = S.make_samples(1000)
+    # empty scene: every pixel black
+    sc = rtb.Scene(np.zeros((0, 9), np.float32), np.zeros((0, 3), np.float32))
+    sc.set_samples(smp)
+    frame, st = sc.render(width=33, height=9)
+    assert frame.shape == (9, 33, 3) and frame.max() == 0 and st["primary_hits"] == 0
+    # single primitive (no inner node): the ground alone
+    sc = rtb.Scene(S.GROUND, S.GROUND_COLOR)
+    sc.set_samples(smp)
+    osc = O.OracleScene(S.GROUND, S.GROUND_COLOR, True)
+    o = osc.render(64, 40, smp, S.EYE, S.LOOK_AT, S.UP, 20.0, S.LIGHT, nb_light_sample=3)
+    frame, st = sc.render(width=64, height=40, distance=20.0, nb_light_sample=3)
+    assert (frame == o["rgb8"]).all() and st["primary_hits"] == o["stats"]["primary_hits"] > 0
+    # no light samples / no rays: black, no shadow rays
+    frame, st = sc.render(width=64, height=40, distance=20.0, nb_light_sample=0)
+    assert frame.max() == 0 and st["shadow_rays"] == 0 and st["primary_hits"] > 0
+    frame, st = sc.render(width=64, height=40, distance=20.0, nb_ray=0)
+    assert frame.max() == 0 and st["primary_rays"] == 0
+    # render before set_samples is a state error, not a crash
+    sc2 = rtb.Scene(S.GROUND, S.GROUND_COLOR)
+    with pytest.raises(rtb.RtbError):
+        sc2.render(width=8, height=8)
+    # degenerate (zero-area) and NaN-normal triangles do not poison their neighbours
+    v = np.concatenate([np.array([[0, 10, -50, 0, 10, -50, 0, 10, -50]], np.float32), S.GROUND])
+    c = np.concatenate([np.ones((1, 3), np.float32), S.GROUND_COLOR])
+    sc3 = rtb.Scene(v, c)
+    sc3.set_samples(smp)
+    o3 = O.OracleScene(v, c, True).render(64, 40, smp, S.EYE, S.LOOK_AT, S.UP, 20.0, S.LIGHT, nb_light_sample=3)
+    f3, _ = sc3.render(width=64, height=40, distance=20.0, nb_light_sample=3)
+    assert (f3 == o3["rgb8"]).all()
+
+
+def test_color_to_u8_every_threshold(gpu_big_bunny):
+    """Color::to_rgba on the device == the oracle's powf path at every byte boundary +-2 ulp, and on random values."""
+    from oracle.oracle import gamma_u8
+    # find each boundary with the oracle, then probe around it on the device
+    probes = []
+    for k in range(1, 256):
+        lo, hi = 0, 0x40000000
+        while lo < hi:
+            mid = (lo + hi) // 2
+            if gamma_u8(np.array([mid], np.uint32).view(np.float32)[0]) >= k:
+                hi = mid
+            else:
+                lo = mid + 1
+        probes += [max(0, lo + d) for d in (-2, -1, 0, 1, 2)]
+    x = np.array(probes, np.uint32).view(np.float32)
+    rnd = np.random.default_rng(0).uniform(0, 1.2, 20000).astype(np.float32)
+    special = np.array([0.0, -0.0, 1.0, 2.0, 1e-30, np.inf, -1.0, np.nan], np.float32)
+    x = np.concatenate([x, rnd, special])
+    got = gpu_big_bunny.color_to_u8(x)
+    want = np.array([gamma_u8(v) for v in x], np.uint8)
+    assert (got == want).all()

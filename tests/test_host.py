@@ -1,0 +1,124 @@
+"""CPU tests of the host side of the boundary: the C-ABI library loads and exports every declared symbol, the
+host entry points kept from main.rs (OBJ import, sample table, PNG save, band ownership) behave like the
+reference, and compute calls fail loudly (never fall back) without a GPU."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import scenes as S
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def rtb(built):
+    import rtb200
+    rtb200.lib()
+    return rtb200
+
+
+def test_library_exports_every_declared_symbol(rtb):
+    hdr = open(os.path.join(ROOT, "include", "rtb200.h")).read()
+    declared = set(re.findall(r"\b(rtb_[a-z_0-9]+)\s*\(", hdr))
+    assert declared == set(rtb.EXPORTS), declared ^ set(rtb.EXPORTS)
+    L = rtb.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+    assert b"sm_100a" in L.rtb_version()
+
+
+def test_struct_layouts_match_header(rtb):
+    import ctypes as C
+    assert C.sizeof(rtb.binding.RenderParams) == 4 * 4 + 10 * 4 + 4 * 4
+    assert C.sizeof(rtb.binding.Stats) == 6 * 8 + 8
+    assert C.sizeof(rtb.binding.SceneDesc) == 8 + 3 * 8 + 9 * 4 + 4
+    assert C.sizeof(rtb.binding.SceneInfo) == 24
+
+
+def test_import_obj_matches_reference_rules(rtb, tmp_path):
+    for name, n in (("big_bunny.obj", 4968), ("bunny.obj", 4968)):
+        path = os.path.join(S.MODELS, name)
+        v = rtb.import_obj(path)
+        assert v.shape == (n, 9)
+        assert (v.view(np.uint32) == S.parse_obj(path).view(np.uint32)).all()
+    # only `v` / `f` lines act; mtllib/usemtl/o/s/comments fall through (src/main.rs:130,137)
+    p = tmp_path / "a.obj"
+    p.write_text("# c\nmtllib x.mtl\no thing\nv 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nusemtl m\ns off\nf 1 2 3\nf 3 2 1")
+    v = rtb.import_obj(str(p))
+    assert v.tolist() == [[0, 0, 0, 1, 0, 0, 0, 1, 0], [0, 1, 0, 1, 0, 0, 0, 0, 0]]
+    # CRLF is stripped by BufRead::lines
+    p.write_text("v 0 0 0\r\nv 1 0 0\r\nv 0 1 0\r\nf 1 2 3\r\n")
+    assert rtb.import_obj(str(p)).shape == (1, 9)
+
+
+def test_import_obj_errors(rtb, tmp_path, capsys):
+    assert rtb.import_obj(str(tmp_path / "missing.obj")).shape == (0, 9)     # prints and continues (src/main.rs:115-121)
+    assert "Not a valid path" in capsys.readouterr().out
+    for bad in ("v 0 0\n", "v 0 0 x\n", "v 0 0 0\nf 1/1 1/1 1/1\n", "v 0 0 0\nf 1 1 2\n", "v 0 0 0\nf 0 1 1\n", "v  0 0 0\n"):
+        p = tmp_path / "bad.obj"
+        p.write_text(bad)
+        with pytest.raises(rtb.RtbError):
+            rtb.import_obj(str(p))                                            # the reference panics (unwrap)
+
+
+def test_fill_samples_matches_documented_generator(rtb):
+    a = rtb.fill_samples(50000)
+    b = S.make_samples(50000)
+    assert (a.view(np.uint32) == b.view(np.uint32)).all()
+    assert a.min() >= 0.0 and a.max() < 1.0
+    assert abs(a.mean() - 0.5) < 0.01
+    assert not (rtb.fill_samples(10, seed=1) == rtb.fill_samples(10, seed=2)).all()
+
+
+def test_write_png_roundtrip(rtb, tmp_path):
+    from PIL import Image
+    rng = np.random.default_rng(0)
+    for (h, w) in ((1, 1), (37, 53), (300, 257)):      # > 65535 bytes: several stored blocks
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        path = str(tmp_path / "o.png")
+        rtb.write_png(path, img)
+        back = np.array(Image.open(path))
+        assert back.shape == img.shape and (back == img).all()
+        assert Image.open(path).mode == "RGB"
+
+
+def test_band_ownership_partitions_the_frame(rtb):
+    for height, band, world in ((1080, 8, 1), (1080, 8, 2), (2160, 8, 8), (1080, 16, 4), (77, 8, 3), (5, 8, 4)):
+        seen = []
+        for r in range(world):
+            rows = rtb.owned_row_indices(height, band, r, world)
+            assert len(rows) == rtb.owned_rows(height, band, r, world)
+            seen.append(rows)
+        allrows = np.sort(np.concatenate(seen))
+        assert (allrows == np.arange(height)).all()
+
+
+def test_create_ground_and_defaults(rtb):
+    v, c = rtb.create_ground()
+    assert (v == S.GROUND).all() and (c == S.GROUND_COLOR).all()
+    assert (rtb.DEFAULT_LIGHT == S.LIGHT).all()
+    assert rtb.DEFAULT_CAMERA["distance"] == 288.0
+
+
+def test_no_cpu_fallback(rtb):
+    """Without a usable CUDA device scene creation must raise, not render on the CPU."""
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except Exception:
+        has_gpu = False
+    if has_gpu:
+        pytest.skip("GPU present")
+    with pytest.raises(rtb.RtbError):
+        rtb.Scene(*S.big_bunny())
+
+
+def test_product_never_touches_the_oracle():
+    pkg = os.path.join(ROOT, "ray-tracer-rust_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".rs", "Makefile")):
+                txt = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "oracle" not in txt.lower().replace("no oracle", ""), os.path.join(dirpath, f)
