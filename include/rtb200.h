@@ -118,6 +118,11 @@ int rtb_color_to_u8(rtb_scene* scene, const float* linear, uint64_t n, uint8_t* 
  * device, or the caller's, or the primitive index (see rtb_scene_desc.tie_rank). */
 int rtb_scene_get_tie_ranks(rtb_scene* scene, int32_t* out);
 
+/* The built BVH, for inspection and structural tests (HOST array of n_nodes * 16 floats).  Node i: floats 0-5 =
+ * child 0 box (lo.xyz, hi.xyz), 6-11 = child 1 box, 12-13 = child indices as int32 bit patterns (>= 0 inner node,
+ * < 0 = ~primitive), 14-15 unused.  Node 0 is the root.  The tree's shape is NOT part of the results contract. */
+int rtb_scene_get_nodes(rtb_scene* scene, float* out);
+
 /* Rows owned by (rank, world) for a frame of `height` rows in bands of band_rows. */
 uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint32_t world);
 

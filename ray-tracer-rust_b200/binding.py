@@ -46,7 +46,7 @@ class SceneInfo(C.Structure):
 
 
 EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_render",
-           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_import_obj",
+           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_import_obj",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
 
 _lib = None
@@ -70,6 +70,7 @@ def lib():
         L.rtb_render_pixels.argtypes = [vp, vp, vp, C.c_uint64, vp, vp, vp, vp, vp, vp]
         L.rtb_color_to_u8.argtypes = [vp, vp, C.c_uint64, vp]
         L.rtb_scene_get_tie_ranks.argtypes = [vp, vp]
+        L.rtb_scene_get_nodes.argtypes = [vp, vp]
         L.rtb_owned_rows.argtypes = [C.c_uint32] * 4; L.rtb_owned_rows.restype = C.c_uint32
         L.rtb_deinterleave_bands.argtypes = [C.c_int32, vp, C.c_uint64, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]
         L.rtb_import_obj.argtypes = [C.c_char_p, vp, vp]
@@ -215,6 +216,13 @@ class Scene:
         out = np.zeros(lin.shape, np.uint8)
         _check(lib().rtb_color_to_u8(self._h, _ptr(lin), lin.size, _ptr(out)))
         return out
+
+    def nodes(self):
+        """(n_nodes, 16) float32 view of the BVH + (n_nodes, 2) int32 children (see rtb_scene_get_nodes)."""
+        n = self.info()["n_nodes"]
+        out = np.zeros((n, 16), np.float32)
+        _check(lib().rtb_scene_get_nodes(self._h, _ptr(out)))
+        return out, out[:, 12:14].copy().view(np.int32)
 
     def tie_ranks(self):
         out = np.zeros(self.verts.shape[0], np.int32)

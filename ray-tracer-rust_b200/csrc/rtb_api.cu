@@ -17,7 +17,7 @@ cudaError_t rtb_build_scene(const float*, const float*, const int*, uint32_t, fl
 cudaError_t rtb_tie_rank_device(const float4* d_tris, uint32_t n, int* d_rank_out, float4* d_colors4, cudaStream_t st);
 cudaError_t rtb_launch_trace_frame(const TraceArgs&, bool, cudaStream_t);
 cudaError_t rtb_launch_trace_list(const TraceArgs&, bool, cudaStream_t);
-cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, cudaStream_t);
+cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, float*, cudaStream_t);
 cudaError_t rtb_launch_deinterleave(const uint8_t*, uint64_t, uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, cudaStream_t);
 cudaError_t rtb_upload_gamma_table(const float*);
 cudaError_t rtb_launch_color_to_u8(const float*, uint64_t, uint8_t*, cudaStream_t);
@@ -41,6 +41,7 @@ struct rtb_scene {
     float2* d_samples; uint32_t n_samples;
     float4* d_light_pts; uint32_t light_pts_cap;
     unsigned long long* d_counters;
+    float* d_light_box;                          // 6 floats, bounds of d_light_pts (k_light_bounds)
     uint8_t* d_frame; size_t frame_cap;          // staging for rtb_render (host output)
     uint8_t* h_pinned; size_t pinned_cap;
     cudaStream_t stream;
@@ -106,7 +107,7 @@ void rtb_scene_destroy(rtb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts);
-    cudaFree(s->d_counters); cudaFree(s->d_frame);
+    cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -140,6 +141,7 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     TRY_(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     TRY_(cudaEventCreate(&s->ev0)); TRY_(cudaEventCreate(&s->ev1));
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
+    TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
     if (n) {
         TRY_(cudaMalloc(&d_verts, (size_t)n * 9 * 4)); TRY_(cudaMalloc(&d_colors, (size_t)n * 3 * 4));
         TRY_(cudaMemcpyAsync(d_verts, desc->verts, (size_t)n * 9 * 4, cudaMemcpyHostToDevice, s->stream));
@@ -206,10 +208,10 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         CUDA_TRY(cudaMalloc(&s->d_light_pts, (size_t)need * sizeof(float4)));
         s->light_pts_cap = (uint32_t)need;
     }
-    CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, st));
+    CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
     memset(a, 0, sizeof(*a));
-    a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts;
+    a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_box = s->d_light_box;
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
     a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;
     a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;
@@ -324,6 +326,15 @@ cleanup:
     cudaFree(d_in); cudaFree(d_out);
     return rc;
 #undef TRY_
+}
+
+int rtb_scene_get_nodes(rtb_scene* s, float* out) {
+    if (!s || !out) return fail(RTB_ERR_ARG, "rtb_scene_get_nodes: null argument");
+    if (s->info.n_nodes == 0) return RTB_OK;
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaMemcpyAsync(out, s->d_nodes, (size_t)s->info.n_nodes * 64, cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return RTB_OK;
 }
 
 int rtb_scene_get_tie_ranks(rtb_scene* s, int32_t* out) {

@@ -43,6 +43,7 @@ struct TraceArgs {
     const float4* __restrict__ nodes;    // 4 float4 per inner node (layout in rtb_bvh.cu)
     const float2* __restrict__ samples;  // n_samples (u,v) pairs
     const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table
+    const float* __restrict__ light_box; // 6 floats: component-wise min / max of light_pts[0..n_light_pts)
     uint32_t n_tris, n_samples, n_light_pts;
     int32_t root;                        // node index, ~prim for a single-primitive scene, RTB_CHILD_NONE if empty
     uint32_t width, height, nb_ray, nb_light_sample;
