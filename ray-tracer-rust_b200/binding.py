@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtb200.so")
+LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(_HERE, "librtb200.so")   # override: kernel-variant experiments
 
 RTB_FLAG_COUNTERS = 1
 
