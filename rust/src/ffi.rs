@@ -1,0 +1,67 @@
+//! extern "C" declarations of include/rtb200.h (librtb200.so, sm_100a CUDA behind a C ABI).
+//! SOURCE ONLY: the build image has no Rust toolchain; the struct layouts are checked against the header by
+//! tests/test_host.py::test_struct_layouts_match_header through the Python mirror of the same structs.
+#![allow(dead_code)]
+use std::os::raw::{c_char, c_void};
+
+pub const RTB_OK: i32 = 0;
+pub const RTB_FLAG_COUNTERS: u32 = 1;
+
+#[repr(C)]
+pub struct RtbScene { _private: [u8; 0] }
+
+#[repr(C)]
+pub struct RtbSceneDesc {
+    pub n_tris: u32,
+    pub verts: *const f32,      // n_tris * 9
+    pub colors: *const f32,     // n_tris * 3
+    pub tie_rank: *const i32,   // optional
+    pub light: [f32; 9],
+    pub device: i32,
+}
+
+#[repr(C)]
+pub struct RtbRenderParams {
+    pub width: u32, pub height: u32, pub nb_ray: u32, pub nb_light_sample: u32,
+    pub eye: [f32; 3], pub look_at: [f32; 3], pub up: [f32; 3], pub distance: f32,
+    pub band_rows: u32, pub rank: u32, pub world: u32, pub flags: u32,
+}
+
+#[repr(C)]
+#[derive(Default)]
+pub struct RtbStats {
+    pub primary_rays: u64, pub primary_hits: u64, pub shadow_rays: u64, pub shadow_occluded: u64,
+    pub box_tests: u64, pub tri_tests: u64, pub kernel_ms: f32, pub launches: u32,
+}
+
+#[repr(C)]
+#[derive(Default)]
+pub struct RtbSceneInfo {
+    pub n_tris: u32, pub n_nodes: u32, pub max_depth: u32, pub ploc_iterations: u32,
+    pub sah_cost: f32, pub build_ms: f32,
+}
+
+#[link(name = "rtb200")]
+extern "C" {
+    pub fn rtb_scene_create(desc: *const RtbSceneDesc, out: *mut *mut RtbScene) -> i32;
+    pub fn rtb_scene_destroy(scene: *mut RtbScene);
+    pub fn rtb_scene_get_info(scene: *const RtbScene, info: *mut RtbSceneInfo) -> i32;
+    pub fn rtb_scene_set_samples(scene: *mut RtbScene, samples: *const f32, n_pairs: u32) -> i32;
+    pub fn rtb_render(scene: *mut RtbScene, params: *const RtbRenderParams, rgb8: *mut u8, stats: *mut RtbStats) -> i32;
+    pub fn rtb_render_device(scene: *mut RtbScene, params: *const RtbRenderParams, d_rgb8: *mut c_void, cuda_stream: *mut c_void) -> i32;
+    pub fn rtb_render_pixels(scene: *mut RtbScene, params: *const RtbRenderParams, pixels: *const u32, n_pix: u64,
+                             rgb_lin: *mut f32, rgb8: *mut u8, hit_count: *mut u8, prim0: *mut i32, t0: *mut f32,
+                             stats: *mut RtbStats) -> i32;
+    pub fn rtb_color_to_u8(scene: *mut RtbScene, linear: *const f32, n: u64, out: *mut u8) -> i32;
+    pub fn rtb_scene_get_tie_ranks(scene: *mut RtbScene, out: *mut i32) -> i32;
+    pub fn rtb_scene_get_nodes(scene: *mut RtbScene, out: *mut f32) -> i32;
+    pub fn rtb_owned_rows(height: u32, band_rows: u32, rank: u32, world: u32) -> u32;
+    pub fn rtb_deinterleave_bands(device: i32, d_staged: *const c_void, stride_bytes: u64, d_frame: *mut c_void,
+                                  width: u32, height: u32, band_rows: u32, world: u32, cuda_stream: *mut c_void) -> i32;
+    pub fn rtb_import_obj(path: *const c_char, verts_out: *mut *mut f32, n_out: *mut u32) -> i32;
+    pub fn rtb_free(p: *mut c_void);
+    pub fn rtb_fill_samples(seed: u64, n_pairs: u32, out: *mut f32);
+    pub fn rtb_write_png(path: *const c_char, rgb8: *const u8, width: u32, height: u32) -> i32;
+    pub fn rtb_last_error() -> *const c_char;
+    pub fn rtb_version() -> *const c_char;
+}
