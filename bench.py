@@ -267,7 +267,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,
                     "h2d_bytes_per_step": int(samples.nbytes + 64), "d2h_bytes_per_step": int(rows * WIDTH * 3),
                     "path": "rtb_scene_set_samples + rtb_render with pinned host buffers"},
-            "gpu_launches": args.steps * (2 * world + (1 if world > 1 else 0)),
+            "gpu_launches": args.steps * (5 * world + (1 if world > 1 else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
                          "traffic": None, "kernel": "k_trace_frame", "kernel_ms": kernel_ms, "algorithmic_flops_per_launch": flops / world,
                          "peak_source": "SMs x 128 FP32 lanes x 2 x SM clock under load (%d SMs, %.0f MHz); MEASURED_PEAKS.json has no FP32 entry"

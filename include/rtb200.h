@@ -69,8 +69,12 @@ typedef struct {
 typedef struct {
     uint64_t primary_rays, primary_hits, shadow_rays, shadow_occluded;
     uint64_t box_tests, tri_tests;   /* only with RTB_FLAG_COUNTERS, else 0 */
-    float kernel_ms;                 /* device time of the trace kernel(s) of this call (CUDA events) */
+    float kernel_ms;                 /* device time of the trace kernels of this call (CUDA events) */
     uint32_t launches;               /* kernels launched by this call */
+    float primary_ms, shadow_ms, shade_ms;   /* k_primary / k_shadow_queue / k_shade, same events */
+    uint32_t queued_hits;            /* hit points whose shadow rays needed the BVH (shadow queue length) */
+    uint32_t queued_walks;           /* ... of which the per-ray BVH walk (not just a candidate list) was needed */
+    uint32_t reserved_;
 } rtb_stats;
 
 typedef struct {

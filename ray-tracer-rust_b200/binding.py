@@ -34,7 +34,8 @@ class RenderParams(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("primary_rays", C.c_uint64), ("primary_hits", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("shadow_occluded", C.c_uint64), ("box_tests", C.c_uint64), ("tri_tests", C.c_uint64),
-                ("kernel_ms", C.c_float), ("launches", C.c_uint32)]
+                ("kernel_ms", C.c_float), ("launches", C.c_uint32), ("primary_ms", C.c_float), ("shadow_ms", C.c_float),
+                ("shade_ms", C.c_float), ("queued_hits", C.c_uint32), ("queued_walks", C.c_uint32), ("reserved_", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -15,9 +15,9 @@
 struct RtbBuildInfo { uint32_t n_nodes, max_depth, iterations; float sah_cost, build_ms; };
 cudaError_t rtb_build_scene(const float*, const float*, const int*, uint32_t, float4*, float4*, float4**, int32_t*, RtbBuildInfo*, cudaStream_t);
 cudaError_t rtb_tie_rank_device(const float4* d_tris, uint32_t n, int* d_rank_out, float4* d_colors4, cudaStream_t st);
-cudaError_t rtb_launch_trace_frame(const TraceArgs&, bool, cudaStream_t);
-cudaError_t rtb_launch_trace_list(const TraceArgs&, bool, cudaStream_t);
+cudaError_t rtb_launch_trace(const TraceArgs&, bool, cudaStream_t, cudaEvent_t*);
 cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, float*, cudaStream_t);
+cudaError_t rtb_launch_light_perm(const float4*, const float*, uint32_t, uint32_t, uint32_t, uint16_t*, cudaStream_t);
 cudaError_t rtb_launch_deinterleave(const uint8_t*, uint64_t, uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, cudaStream_t);
 cudaError_t rtb_upload_gamma_table(const float*);
 cudaError_t rtb_launch_color_to_u8(const float*, uint64_t, uint8_t*, cudaStream_t);
@@ -40,12 +40,17 @@ struct rtb_scene {
     RtbBuildInfo info;
     float2* d_samples; uint32_t n_samples;
     float4* d_light_pts; uint32_t light_pts_cap;
+    uint16_t* d_light_perm; size_t light_perm_cap;
     unsigned long long* d_counters;
     float* d_light_box;                          // 6 floats, bounds of d_light_pts (k_light_bounds)
     uint8_t* d_frame; size_t frame_cap;          // staging for rtb_render (host output)
+    // wavefront buffers, grown on demand and kept (see rtb_trace.cu)
+    uint2* d_records; float4* d_items; uint32_t* d_masks; uint32_t* d_queue_ctl;
+    size_t rays_cap, mask_cap;
     uint8_t* h_pinned; size_t pinned_cap;
     cudaStream_t stream;
     cudaEvent_t ev0, ev1;
+    cudaEvent_t evk[2];                          // between the wavefront kernels (per-kernel times in rtb_stats)
 };
 
 // ---- Color::to_rgba threshold table (color.rs:10-33) ---------------------------------------
@@ -106,11 +111,13 @@ uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint
 void rtb_scene_destroy(rtb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts);
+    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm);
     cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame);
+    cudaFree(s->d_records); cudaFree(s->d_items); cudaFree(s->d_masks); cudaFree(s->d_queue_ctl);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
+    for (int k = 0; k < 2; ++k) if (s->evk[k]) cudaEventDestroy(s->evk[k]);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -140,8 +147,10 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
 #define TRY_(x) do { e = (x); if (e != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e)); goto cleanup; } } while (0)
     TRY_(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     TRY_(cudaEventCreate(&s->ev0)); TRY_(cudaEventCreate(&s->ev1));
+    TRY_(cudaEventCreate(&s->evk[0])); TRY_(cudaEventCreate(&s->evk[1]));
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
+    TRY_(cudaMalloc(&s->d_queue_ctl, 4 * sizeof(uint32_t)));
     if (n) {
         TRY_(cudaMalloc(&d_verts, (size_t)n * 9 * 4)); TRY_(cudaMalloc(&d_colors, (size_t)n * 3 * 4));
         TRY_(cudaMemcpyAsync(d_verts, desc->verts, (size_t)n * 9 * 4, cudaMemcpyHostToDevice, s->stream));
@@ -209,9 +218,18 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         s->light_pts_cap = (uint32_t)need;
     }
     CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
+    const size_t perm_need = (size_t)p->nb_ray * p->nb_light_sample;
+    const bool use_perm = perm_need > 0 && p->nb_light_sample <= 2048;
+    if (use_perm && perm_need > s->light_perm_cap) {
+        cudaFree(s->d_light_perm); s->d_light_perm = nullptr; s->light_perm_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_light_perm, perm_need * sizeof(uint16_t)));
+        s->light_perm_cap = perm_need;
+    }
+    if (use_perm) CUDA_TRY(rtb_launch_light_perm(s->d_light_pts, s->d_light_box, p->nb_ray, p->nb_light_sample, s->n_samples, s->d_light_perm, st));
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
     memset(a, 0, sizeof(*a));
     a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_box = s->d_light_box;
+    a->light_perm = use_perm ? s->d_light_perm : nullptr;
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
     a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;
     a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;
@@ -222,16 +240,62 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     return RTB_OK;
 }
 
+// Sizes the wavefront buffers for n_pix_padded pixels x nb_ray rays (worst case: every ray hits and is queued) and
+// resets the queue.  Frame mode: a.pixel_list == nullptr, tiles of 8x4 pixels; list mode: a.n_pix listed pixels.
+static int prepare_wavefront(rtb_scene* s, cudaStream_t st, TraceArgs* a) {
+    uint64_t npp;
+    if (a->pixel_list) {
+        npp = (a->n_pix + 255) / 256 * 256;
+        a->tiles_x = 0;
+    } else {
+        a->tiles_x = (a->width + 7) / 8;
+        const uint64_t tiles = (uint64_t)a->tiles_x * ((a->owned_rows + 3) / 4);
+        npp = (tiles * 32 + 255) / 256 * 256;
+    }
+    const uint64_t rays = npp * a->nb_ray;
+    if (rays >= 0x7fffffffull) return fail(RTB_ERR_LIMIT, "render: %llu rays in one call exceed the 2^31 record index", (unsigned long long)rays);
+    a->n_pix_padded = (uint32_t)npp;
+    a->mask_words = (a->nb_light_sample + 31) / 32;
+    if (rays > s->rays_cap) {
+        cudaFree(s->d_records); cudaFree(s->d_items); s->d_records = nullptr; s->d_items = nullptr; s->rays_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_records, rays * sizeof(uint2)));
+        CUDA_TRY(cudaMalloc(&s->d_items, rays * RTB_ITEM_F4 * sizeof(float4)));
+        s->rays_cap = rays;
+    }
+    const uint64_t mask_need = rays * a->mask_words;
+    if (mask_need > s->mask_cap) {
+        cudaFree(s->d_masks); s->d_masks = nullptr; s->mask_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_masks, (mask_need ? mask_need : 1) * sizeof(uint32_t)));
+        s->mask_cap = mask_need;
+    }
+    CUDA_TRY(cudaMemsetAsync(s->d_queue_ctl, 0, 4 * sizeof(uint32_t), st));
+    a->records = s->d_records; a->items = s->d_items; a->masks = s->d_masks; a->queue_ctl = s->d_queue_ctl;
+    a->queue_ticket = (unsigned long long*)(s->d_queue_ctl + 2);
+    return RTB_OK;
+}
+
 static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix, float ms, uint32_t launches, rtb_stats* st) {
+    float k_ms[3] = {0.0f, 0.0f, 0.0f};
     unsigned long long h[RTB_NUM_CTRS];
     CUDA_TRY(cudaMemcpyAsync(h, s->d_counters, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     if (h[RTB_CTR_OVERFLOW]) return fail(RTB_ERR_LIMIT, "traversal stack overflow");
+    if (launches >= 5) {
+        CUDA_TRY(cudaEventElapsedTime(&k_ms[0], s->ev0, s->evk[0]));
+        CUDA_TRY(cudaEventElapsedTime(&k_ms[1], s->evk[0], s->evk[1]));
+        CUDA_TRY(cudaEventElapsedTime(&k_ms[2], s->evk[1], s->ev1));
+    }
     if (st) {
         st->primary_rays = n_pix * p->nb_ray; st->primary_hits = h[RTB_CTR_PRIMARY_HITS];
         st->shadow_rays = h[RTB_CTR_SHADOW]; st->shadow_occluded = h[RTB_CTR_OCCLUDED];
         st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
         st->kernel_ms = ms; st->launches = launches;
+        st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];
+        unsigned int qc[2] = {0, 0};
+        CUDA_TRY(cudaMemcpy(qc, s->d_queue_ctl, sizeof(qc), cudaMemcpyDeviceToHost));
+        st->queued_hits = launches >= 5 ? qc[0] : 0;
+        st->queued_walks = launches >= 5 ? qc[1] : 0;
+        st->reserved_ = (uint32_t)h[6];
     }
     return RTB_OK;
 }
@@ -245,7 +309,9 @@ int rtb_render_device(rtb_scene* s, const rtb_render_params* p, void* d_rgb8, vo
     if (rc != RTB_OK) return rc;
     if (!d_rgb8) return fail(RTB_ERR_ARG, "rtb_render_device: null output");
     a.rgb8 = (uint8_t*)d_rgb8;
-    CUDA_TRY(rtb_launch_trace_frame(a, (p->flags & RTB_FLAG_COUNTERS) != 0, st));
+    rc = prepare_wavefront(s, st, &a);
+    if (rc != RTB_OK) return rc;
+    CUDA_TRY(rtb_launch_trace(a, (p->flags & RTB_FLAG_COUNTERS) != 0, st, nullptr));
     return RTB_OK;
 }
 
@@ -261,14 +327,16 @@ int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stat
         s->frame_cap = bytes;
     }
     a.rgb8 = s->d_frame;
+    rc = prepare_wavefront(s, s->stream, &a);
+    if (rc != RTB_OK) return rc;
     CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
-    CUDA_TRY(rtb_launch_trace_frame(a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream));
+    CUDA_TRY(rtb_launch_trace(a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, s->evk));
     CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
     if (bytes) CUDA_TRY(cudaMemcpyAsync(rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     float ms = 0.0f;
     CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 2, stats);
+    return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 5, stats);
 }
 
 int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* pixels, uint64_t n_pix, float* rgb_lin,
@@ -291,8 +359,12 @@ int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* 
         if (t0) TRY_(cudaMalloc(&d_t0, n_pix * 4));
     }
     a.pixel_list = d_pix; a.n_pix = n_pix; a.out_rgb_lin = d_lin; a.rgb8 = d_rgb8; a.out_hit_count = d_hc; a.out_prim0 = d_p0; a.out_t0 = d_t0;
+    if (n_pix) {
+        rc = prepare_wavefront(s, s->stream, &a);
+        if (rc != RTB_OK) goto cleanup;
+    }
     TRY_(cudaEventRecord(s->ev0, s->stream));
-    TRY_(rtb_launch_trace_list(a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream));
+    if (n_pix) TRY_(rtb_launch_trace(a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, s->evk));
     TRY_(cudaEventRecord(s->ev1, s->stream));
     if (n_pix) {
         if (rgb_lin) TRY_(cudaMemcpyAsync(rgb_lin, d_lin, n_pix * 12, cudaMemcpyDeviceToHost, s->stream));
@@ -303,7 +375,7 @@ int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* 
     }
     TRY_(cudaStreamSynchronize(s->stream));
     TRY_(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    rc = fetch_stats(s, p, n_pix, ms, 2, stats);
+    rc = fetch_stats(s, p, n_pix, ms, n_pix ? 5 : 2, stats);
 cleanup:
     cudaFree(d_pix); cudaFree(d_lin); cudaFree(d_rgb8); cudaFree(d_hc); cudaFree(d_p0); cudaFree(d_t0);
     return rc;

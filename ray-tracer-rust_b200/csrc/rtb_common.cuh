@@ -12,6 +12,10 @@
 
 #define RTB_STACK_SIZE 64          // traversal stack entries (binary BVH depth limit)
 #define RTB_CHILD_NONE 0x7fffffff  // absent child (single-primitive scenes)
+#ifndef RTB_MAX_CAND
+#define RTB_MAX_CAND 8             // primitives a hit point's shadow rays test directly (multiple of 4)
+#endif
+#define RTB_ITEM_F4 (2 + RTB_MAX_CAND / 4)   // float4 per shadow-queue item: {ray id, prim word, entry, n_cand} {p_hit} {cand...}
 
 struct f3 { float x, y, z; };
 
@@ -44,15 +48,23 @@ struct TraceArgs {
     const float2* __restrict__ samples;  // n_samples (u,v) pairs
     const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table
     const float* __restrict__ light_box; // 6 floats: component-wise min / max of light_pts[0..n_light_pts)
+    const uint16_t* __restrict__ light_perm; // [nb_ray][nb_light_sample] lane order of the shadow queue (k_light_perm), or nullptr
     uint32_t n_tris, n_samples, n_light_pts;
     int32_t root;                        // node index, ~prim for a single-primitive scene, RTB_CHILD_NONE if empty
     uint32_t width, height, nb_ray, nb_light_sample;
     uint32_t band_rows, rank, world, owned_rows;
     CameraBasis cam;
     float denom;                         // (NB_RAY * NB_LIGHT_SAMPLE) as f32 (src/main.rs:211)
+    // wavefront buffers (rtb_trace.cu): hit records [nb_ray][n_pix_padded], shadow queue, occlusion masks
+    uint2* records;                      // {t bits, prim | flags} per (ray r, padded pixel)
+    float4* items;                       // 3 float4 per queued hit point
+    uint32_t* masks;                     // mask_words per queued hit point: bit i = light sample i occluded
+    uint32_t* queue_ctl;                 // [0] items appended by k_primary
+    unsigned long long* queue_ticket;    // next unclaimed (item, sample) ray of k_shadow_queue
+    uint32_t n_pix_padded, tiles_x, mask_words;
     // outputs
-    uint8_t* rgb8;                       // frame mode: owned rows, compact
-    const uint2* pixel_list;             // list mode
+    uint8_t* rgb8;                       // frame mode: owned rows, compact; list mode: 3 bytes per listed pixel
+    const uint2* pixel_list;             // list mode (else nullptr)
     uint64_t n_pix;
     float* out_rgb_lin; uint8_t* out_hit_count; int32_t* out_prim0; float* out_t0;
     unsigned long long* counters;        // [0] primary hits [1] shadow rays [2] occluded [3] box tests [4] tri tests [5] stack overflow

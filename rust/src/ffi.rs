@@ -32,6 +32,8 @@ pub struct RtbRenderParams {
 pub struct RtbStats {
     pub primary_rays: u64, pub primary_hits: u64, pub shadow_rays: u64, pub shadow_occluded: u64,
     pub box_tests: u64, pub tri_tests: u64, pub kernel_ms: f32, pub launches: u32,
+    pub primary_ms: f32, pub shadow_ms: f32, pub shade_ms: f32, pub queued_hits: u32,
+    pub queued_walks: u32, pub reserved_: u32,
 }
 
 #[repr(C)]

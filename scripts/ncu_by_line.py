@@ -13,7 +13,7 @@ for ln in dis:
     if not infn: continue
     m = re.match(r'\s*//## File "([^"]+)", line (\d+)(.*)', ln)
     if m:
-        if pending is None: pending = int(m.group(2))     # innermost frame comes first
+        if pending is None: pending = (m.group(1).split('/')[-1], int(m.group(2)))     # innermost frame comes first
         continue
     m = re.match(r"\s*/\*([0-9a-f]{4,})\*/", ln)
     if m:
@@ -29,8 +29,18 @@ for r in rows[hi + 1:]:
     if base is None: base = a
     l = line_of.get(a - base)
     per[l] += n; thr[l] += t; smp[l] += s; tot += n
-text = open(srcfile).read().splitlines() if srcfile else []
+import os
+texts = {}
+def src_line(key):
+    if not key or not srcfile: return ""
+    f, l = key
+    if f not in texts:
+        path = os.path.join(os.path.dirname(srcfile), f)
+        texts[f] = open(path).read().splitlines() if os.path.exists(path) else []
+    t = texts[f]
+    return t[l - 1].strip()[:100] if 0 < l <= len(t) else ""
 print("total warp instructions %d" % tot)
 for l, n in per.most_common(top):
-    code = text[l - 1].strip()[:100] if l and l <= len(text) else ""
-    print("%5.1f%%  thr %4.1f  smp %5.1f%%  L%-4s %s" % (100.0 * n / tot, thr[l] / max(n, 1), 100.0 * smp[l] / max(sum(smp.values()), 1), l, code))
+    code = src_line(l)
+    tag = "%s:%d" % (l[0].replace("rtb_", "").replace(".cuh", "").replace(".cu", ""), l[1]) if l else "?"
+    print("%5.1f%%  thr %4.1f  smp %5.1f%%  %-11s %s" % (100.0 * n / tot, thr[l] / max(n, 1), 100.0 * smp[l] / max(sum(smp.values()), 1), tag, code))
