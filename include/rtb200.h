@@ -71,10 +71,10 @@ typedef struct {
     uint64_t box_tests, tri_tests;   /* only with RTB_FLAG_COUNTERS, else 0 */
     float kernel_ms;                 /* device time of the trace kernels of this call (CUDA events) */
     uint32_t launches;               /* kernels launched by this call */
-    float primary_ms, shadow_ms, shade_ms;   /* k_primary / k_shadow_queue / k_shade, same events */
+    float primary_ms, shadow_ms, shade_ms;   /* k_primary / k_shadow_plan + k_shadow_queue / k_shade, same events */
     uint32_t queued_hits;            /* hit points whose shadow rays needed the BVH (shadow queue length) */
-    uint32_t queued_walks;           /* ... of which the per-ray BVH walk (not just a candidate list) was needed */
-    uint32_t reserved_;
+    uint32_t queued_groups;          /* (hit point, light-sample group) pairs left after the per-group bundle test */
+    uint32_t queued_walks;           /* ... of which need a per-ray BVH walk (not just a short candidate list) */
 } rtb_stats;
 
 typedef struct {
@@ -117,6 +117,10 @@ int rtb_render_pixels(rtb_scene* scene, const rtb_render_params* params, const u
 /* --- replaces Color::to_rgba (src/tracer/utils/color.rs:26-33) on its own: n linear f32 values (HOST) -> n bytes
  *     (HOST), computed by the same device code the trace kernel's epilogue uses. */
 int rtb_color_to_u8(rtb_scene* scene, const float* linear, uint64_t n, uint8_t* out);
+
+/* Device self-test: the shared-reciprocal divisions of the trace kernels (csrc/rtb_trace.cu, div3_exact / div_by) against
+ * the compiler's IEEE `/` on n pseudo-random operand sets; *mismatches must come back 0. */
+int rtb_selftest_division(rtb_scene* scene, uint64_t seed, uint64_t n, uint64_t* mismatches);
 
 /* The tie ranks in use (HOST array of n_tris int32): the leaf order of the reference's tree as replayed on the
  * device, or the caller's, or the primitive index (see rtb_scene_desc.tie_rank). */

@@ -35,7 +35,7 @@ class Stats(C.Structure):
     _fields_ = [("primary_rays", C.c_uint64), ("primary_hits", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("shadow_occluded", C.c_uint64), ("box_tests", C.c_uint64), ("tri_tests", C.c_uint64),
                 ("kernel_ms", C.c_float), ("launches", C.c_uint32), ("primary_ms", C.c_float), ("shadow_ms", C.c_float),
-                ("shade_ms", C.c_float), ("queued_hits", C.c_uint32), ("queued_walks", C.c_uint32), ("reserved_", C.c_uint32)]
+                ("shade_ms", C.c_float), ("queued_hits", C.c_uint32), ("queued_groups", C.c_uint32), ("queued_walks", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -47,7 +47,7 @@ class SceneInfo(C.Structure):
 
 
 EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_render",
-           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_import_obj",
+           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_import_obj",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
 
 _lib = None
@@ -72,6 +72,7 @@ def lib():
         L.rtb_color_to_u8.argtypes = [vp, vp, C.c_uint64, vp]
         L.rtb_scene_get_tie_ranks.argtypes = [vp, vp]
         L.rtb_scene_get_nodes.argtypes = [vp, vp]
+        L.rtb_selftest_division.argtypes = [vp, C.c_uint64, C.c_uint64, vp]
         L.rtb_owned_rows.argtypes = [C.c_uint32] * 4; L.rtb_owned_rows.restype = C.c_uint32
         L.rtb_deinterleave_bands.argtypes = [C.c_int32, vp, C.c_uint64, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]
         L.rtb_import_obj.argtypes = [C.c_char_p, vp, vp]
@@ -224,6 +225,12 @@ class Scene:
         out = np.zeros((n, 16), np.float32)
         _check(lib().rtb_scene_get_nodes(self._h, _ptr(out)))
         return out, out[:, 12:14].copy().view(np.int32)
+
+    def selftest_division(self, n=1 << 26, seed=1):
+        """Mismatches between the kernels' shared-reciprocal division and IEEE `/` over n random operand sets (must be 0)."""
+        bad = C.c_uint64(0)
+        _check(lib().rtb_selftest_division(self._h, seed, n, C.byref(bad)))
+        return bad.value
 
     def tie_ranks(self):
         out = np.zeros(self.verts.shape[0], np.int32)

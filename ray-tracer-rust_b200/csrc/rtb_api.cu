@@ -17,11 +17,12 @@ cudaError_t rtb_build_scene(const float*, const float*, const int*, uint32_t, fl
 cudaError_t rtb_tie_rank_device(const float4* d_tris, uint32_t n, int* d_rank_out, float4* d_colors4, cudaStream_t st);
 cudaError_t rtb_launch_trace(const TraceArgs&, bool, cudaStream_t, cudaEvent_t*);
 cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, float*, cudaStream_t);
-cudaError_t rtb_launch_light_perm(const float4*, const float*, uint32_t, uint32_t, uint32_t, uint16_t*, cudaStream_t);
+cudaError_t rtb_launch_light_groups(const float4*, const float*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint16_t*, float*, cudaStream_t);
 cudaError_t rtb_launch_deinterleave(const uint8_t*, uint64_t, uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, cudaStream_t);
 cudaError_t rtb_upload_gamma_table(const float*);
 cudaError_t rtb_launch_color_to_u8(const float*, uint64_t, uint8_t*, cudaStream_t);
 cudaError_t rtb_launch_get_ranks(const float4*, uint32_t, int*, cudaStream_t);
+cudaError_t rtb_launch_div_selftest(uint64_t, uint64_t, unsigned long long*, cudaStream_t);
 
 static thread_local char g_err[512] = "";
 
@@ -41,6 +42,8 @@ struct rtb_scene {
     float2* d_samples; uint32_t n_samples;
     float4* d_light_pts; uint32_t light_pts_cap;
     uint16_t* d_light_perm; size_t light_perm_cap;
+    float* d_light_gbox; size_t light_gbox_cap;
+    float4* d_subitems; size_t sub_cap;
     unsigned long long* d_counters;
     float* d_light_box;                          // 6 floats, bounds of d_light_pts (k_light_bounds)
     uint8_t* d_frame; size_t frame_cap;          // staging for rtb_render (host output)
@@ -111,7 +114,7 @@ uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint
 void rtb_scene_destroy(rtb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm);
+    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm); cudaFree(s->d_light_gbox); cudaFree(s->d_subitems);
     cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame);
     cudaFree(s->d_records); cudaFree(s->d_items); cudaFree(s->d_masks); cudaFree(s->d_queue_ctl);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
@@ -150,7 +153,7 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     TRY_(cudaEventCreate(&s->evk[0])); TRY_(cudaEventCreate(&s->evk[1]));
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
-    TRY_(cudaMalloc(&s->d_queue_ctl, 4 * sizeof(uint32_t)));
+    TRY_(cudaMalloc(&s->d_queue_ctl, 8 * sizeof(uint32_t)));
     if (n) {
         TRY_(cudaMalloc(&d_verts, (size_t)n * 9 * 4)); TRY_(cudaMalloc(&d_colors, (size_t)n * 3 * 4));
         TRY_(cudaMemcpyAsync(d_verts, desc->verts, (size_t)n * 9 * 4, cudaMemcpyHostToDevice, s->stream));
@@ -218,6 +221,12 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         s->light_pts_cap = (uint32_t)need;
     }
     CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
+    // light-sample groups (k_light_groups): at most RTB_MAX_GROUPS runs of the Hilbert-sorted samples, ~32 samples each
+    uint32_t n_groups = (p->nb_light_sample + 31) / 32;
+    if (n_groups > RTB_MAX_GROUPS) n_groups = RTB_MAX_GROUPS;
+    if (n_groups == 0) n_groups = 1;
+    uint32_t group_size = (p->nb_light_sample + n_groups - 1) / n_groups;
+    if (group_size == 0) group_size = 1;          // nb_light_sample == 0: no shadow rays at all
     const size_t perm_need = (size_t)p->nb_ray * p->nb_light_sample;
     const bool use_perm = perm_need > 0 && p->nb_light_sample <= 2048;
     if (use_perm && perm_need > s->light_perm_cap) {
@@ -225,11 +234,19 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         CUDA_TRY(cudaMalloc(&s->d_light_perm, perm_need * sizeof(uint16_t)));
         s->light_perm_cap = perm_need;
     }
-    if (use_perm) CUDA_TRY(rtb_launch_light_perm(s->d_light_pts, s->d_light_box, p->nb_ray, p->nb_light_sample, s->n_samples, s->d_light_perm, st));
+    const size_t gbox_need = (size_t)p->nb_ray * n_groups * 6;
+    if (gbox_need > s->light_gbox_cap) {
+        cudaFree(s->d_light_gbox); s->d_light_gbox = nullptr; s->light_gbox_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_light_gbox, gbox_need * sizeof(float)));
+        s->light_gbox_cap = gbox_need;
+    }
+    CUDA_TRY(rtb_launch_light_groups(s->d_light_pts, s->d_light_box, p->nb_ray, p->nb_light_sample, s->n_samples, n_groups, group_size,
+                                     use_perm ? s->d_light_perm : nullptr, s->d_light_gbox, st));
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
     memset(a, 0, sizeof(*a));
     a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_box = s->d_light_box;
     a->light_perm = use_perm ? s->d_light_perm : nullptr;
+    a->light_gbox = s->d_light_gbox; a->n_groups = n_groups; a->group_size = group_size;
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
     a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;
     a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;
@@ -262,14 +279,20 @@ static int prepare_wavefront(rtb_scene* s, cudaStream_t st, TraceArgs* a) {
         CUDA_TRY(cudaMalloc(&s->d_items, rays * RTB_ITEM_F4 * sizeof(float4)));
         s->rays_cap = rays;
     }
+    const uint64_t sub_need = rays * a->n_groups;
+    if (sub_need > s->sub_cap) {
+        cudaFree(s->d_subitems); s->d_subitems = nullptr; s->sub_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_subitems, (sub_need ? sub_need : 1) * RTB_SUB_F4 * sizeof(float4)));
+        s->sub_cap = sub_need;
+    }
     const uint64_t mask_need = rays * a->mask_words;
     if (mask_need > s->mask_cap) {
         cudaFree(s->d_masks); s->d_masks = nullptr; s->mask_cap = 0;
         CUDA_TRY(cudaMalloc(&s->d_masks, (mask_need ? mask_need : 1) * sizeof(uint32_t)));
         s->mask_cap = mask_need;
     }
-    CUDA_TRY(cudaMemsetAsync(s->d_queue_ctl, 0, 4 * sizeof(uint32_t), st));
-    a->records = s->d_records; a->items = s->d_items; a->masks = s->d_masks; a->queue_ctl = s->d_queue_ctl;
+    CUDA_TRY(cudaMemsetAsync(s->d_queue_ctl, 0, 8 * sizeof(uint32_t), st));
+    a->records = s->d_records; a->items = s->d_items; a->masks = s->d_masks; a->queue_ctl = s->d_queue_ctl; a->subitems = s->d_subitems;
     a->queue_ticket = (unsigned long long*)(s->d_queue_ctl + 2);
     return RTB_OK;
 }
@@ -280,7 +303,7 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
     CUDA_TRY(cudaMemcpyAsync(h, s->d_counters, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     if (h[RTB_CTR_OVERFLOW]) return fail(RTB_ERR_LIMIT, "traversal stack overflow");
-    if (launches >= 5) {
+    if (launches >= 7) {
         CUDA_TRY(cudaEventElapsedTime(&k_ms[0], s->ev0, s->evk[0]));
         CUDA_TRY(cudaEventElapsedTime(&k_ms[1], s->evk[0], s->evk[1]));
         CUDA_TRY(cudaEventElapsedTime(&k_ms[2], s->evk[1], s->ev1));
@@ -291,11 +314,11 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
         st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
         st->kernel_ms = ms; st->launches = launches;
         st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];
-        unsigned int qc[2] = {0, 0};
+        unsigned int qc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         CUDA_TRY(cudaMemcpy(qc, s->d_queue_ctl, sizeof(qc), cudaMemcpyDeviceToHost));
-        st->queued_hits = launches >= 5 ? qc[0] : 0;
-        st->queued_walks = launches >= 5 ? qc[1] : 0;
-        st->reserved_ = (uint32_t)h[6];
+        st->queued_hits = launches >= 7 ? qc[0] : 0;
+        st->queued_walks = launches >= 7 ? qc[5] : 0;
+        st->queued_groups = launches >= 7 ? qc[4] : 0;
     }
     return RTB_OK;
 }
@@ -336,7 +359,7 @@ int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stat
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     float ms = 0.0f;
     CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 5, stats);
+    return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 7, stats);
 }
 
 int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* pixels, uint64_t n_pix, float* rgb_lin,
@@ -375,7 +398,7 @@ int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* 
     }
     TRY_(cudaStreamSynchronize(s->stream));
     TRY_(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    rc = fetch_stats(s, p, n_pix, ms, n_pix ? 5 : 2, stats);
+    rc = fetch_stats(s, p, n_pix, ms, n_pix ? 7 : 3, stats);
 cleanup:
     cudaFree(d_pix); cudaFree(d_lin); cudaFree(d_rgb8); cudaFree(d_hc); cudaFree(d_p0); cudaFree(d_t0);
     return rc;
@@ -420,6 +443,19 @@ int rtb_scene_get_tie_ranks(rtb_scene* s, int32_t* out) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
     cudaFree(d);
     if (e != cudaSuccess) return fail(RTB_ERR_CUDA, "rtb_scene_get_tie_ranks: %s", cudaGetErrorString(e));
+    return RTB_OK;
+}
+
+int rtb_selftest_division(rtb_scene* s, uint64_t seed, uint64_t n, uint64_t* mismatches) {
+    if (!s || !mismatches) return fail(RTB_ERR_ARG, "rtb_selftest_division: null argument");
+    if (n > 0xffffffffull * 256) return fail(RTB_ERR_ARG, "rtb_selftest_division: n too large");
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), s->stream));
+    CUDA_TRY(rtb_launch_div_selftest(seed, n, s->d_counters, s->stream));
+    unsigned long long h = 0;
+    CUDA_TRY(cudaMemcpyAsync(&h, s->d_counters, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    *mismatches = h;
     return RTB_OK;
 }
 

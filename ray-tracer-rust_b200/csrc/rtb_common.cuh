@@ -15,7 +15,9 @@
 #ifndef RTB_MAX_CAND
 #define RTB_MAX_CAND 8             // primitives a hit point's shadow rays test directly (multiple of 4)
 #endif
-#define RTB_ITEM_F4 (2 + RTB_MAX_CAND / 4)   // float4 per shadow-queue item: {ray id, prim word, entry, n_cand} {p_hit} {cand...}
+#define RTB_ITEM_F4 2                        // float4 per queued hit point: {ray id, prim word, -, -} {p_hit}
+#define RTB_SUB_F4 (1 + RTB_MAX_CAND / 4)    // float4 per shadow sub-item: {hit slot, group, entry, n_cand} {cand...}
+#define RTB_MAX_GROUPS 8                     // light-sample groups per hit point (k_light_groups)
 
 struct f3 { float x, y, z; };
 
@@ -48,7 +50,9 @@ struct TraceArgs {
     const float2* __restrict__ samples;  // n_samples (u,v) pairs
     const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table
     const float* __restrict__ light_box; // 6 floats: component-wise min / max of light_pts[0..n_light_pts)
-    const uint16_t* __restrict__ light_perm; // [nb_ray][nb_light_sample] lane order of the shadow queue (k_light_perm), or nullptr
+    const uint16_t* __restrict__ light_perm; // [nb_ray][nb_light_sample] sample at sorted position j (k_light_groups), nullptr = identity
+    const float* __restrict__ light_gbox;    // [nb_ray][n_groups][6] bounds of each run of group_size sorted samples
+    uint32_t n_groups, group_size;
     uint32_t n_tris, n_samples, n_light_pts;
     int32_t root;                        // node index, ~prim for a single-primitive scene, RTB_CHILD_NONE if empty
     uint32_t width, height, nb_ray, nb_light_sample;
@@ -57,10 +61,11 @@ struct TraceArgs {
     float denom;                         // (NB_RAY * NB_LIGHT_SAMPLE) as f32 (src/main.rs:211)
     // wavefront buffers (rtb_trace.cu): hit records [nb_ray][n_pix_padded], shadow queue, occlusion masks
     uint2* records;                      // {t bits, prim | flags} per (ray r, padded pixel)
-    float4* items;                       // 3 float4 per queued hit point
+    float4* items;                       // RTB_ITEM_F4 float4 per queued hit point
+    float4* subitems;                    // RTB_SUB_F4 float4 per (queued hit point, light-sample group) that can be occluded
     uint32_t* masks;                     // mask_words per queued hit point: bit i = light sample i occluded
-    uint32_t* queue_ctl;                 // [0] items appended by k_primary
-    unsigned long long* queue_ticket;    // next unclaimed (item, sample) ray of k_shadow_queue
+    uint32_t* queue_ctl;                 // [0] hit points queued by k_primary [1] k_shadow_plan ticket [4] sub-items [5] of which need a BVH walk
+    unsigned long long* queue_ticket;    // (= queue_ctl + 2) next unclaimed ray of k_shadow_queue
     uint32_t n_pix_padded, tiles_x, mask_words;
     // outputs
     uint8_t* rgb8;                       // frame mode: owned rows, compact; list mode: 3 bytes per listed pixel

@@ -33,7 +33,7 @@ pub struct RtbStats {
     pub primary_rays: u64, pub primary_hits: u64, pub shadow_rays: u64, pub shadow_occluded: u64,
     pub box_tests: u64, pub tri_tests: u64, pub kernel_ms: f32, pub launches: u32,
     pub primary_ms: f32, pub shadow_ms: f32, pub shade_ms: f32, pub queued_hits: u32,
-    pub queued_walks: u32, pub reserved_: u32,
+    pub queued_groups: u32, pub queued_walks: u32,
 }
 
 #[repr(C)]
@@ -55,6 +55,7 @@ extern "C" {
                              rgb_lin: *mut f32, rgb8: *mut u8, hit_count: *mut u8, prim0: *mut i32, t0: *mut f32,
                              stats: *mut RtbStats) -> i32;
     pub fn rtb_color_to_u8(scene: *mut RtbScene, linear: *const f32, n: u64, out: *mut u8) -> i32;
+    pub fn rtb_selftest_division(scene: *mut RtbScene, seed: u64, n: u64, mismatches: *mut u64) -> i32;
     pub fn rtb_scene_get_tie_ranks(scene: *mut RtbScene, out: *mut i32) -> i32;
     pub fn rtb_scene_get_nodes(scene: *mut RtbScene, out: *mut f32) -> i32;
     pub fn rtb_owned_rows(height: u32, band_rows: u32, rank: u32, world: u32) -> u32;

@@ -23,5 +23,5 @@ for (w, h, nr) in ((1920, 1080, 1), (3840, 2160, 16)):
     for it in range(4):
         img, st = sc.render(width=w, height=h, nb_ray=nr)
         if best is None or st["kernel_ms"] < best["kernel_ms"]: best = st
-    print("%s %dx%d spp%d: total %.2f ms  primary %.2f  shadow %.2f  shade %.2f  queued %d (walks %d) of %d hits" % (
-        tag, w, h, nr, best["kernel_ms"], best["primary_ms"], best["shadow_ms"], best["shade_ms"], best["queued_hits"], best["queued_walks"], best["primary_hits"]), flush=True)
+    print("%s %dx%d spp%d: total %.2f ms  primary %.2f  shadow %.2f  shade %.2f  queued %d hits -> %d sub-items (%d walks) of %d hits" % (
+        tag, w, h, nr, best["kernel_ms"], best["primary_ms"], best["shadow_ms"], best["shade_ms"], best["queued_hits"], best["queued_groups"], best["queued_walks"], best["primary_hits"]), flush=True)

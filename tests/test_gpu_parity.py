@@ -252,3 +252,10 @@ def test_color_to_u8_every_threshold(gpu_big_bunny):
     got = gpu_big_bunny.color_to_u8(x)
     want = np.array([gamma_u8(v) for v in x], np.uint8)
     assert (got == want).all()
+
+
+def test_shared_reciprocal_division_is_ieee(gpu_big_bunny):
+    """div3_exact / div_by (k_shade, k_shadow_queue) must equal the IEEE quotient bit for bit: 2^28 random operand sets
+    with exponents on both sides of the fast-path range and extreme mantissas."""
+    for seed in (1, 2):
+        assert gpu_big_bunny.selftest_division(1 << 27, seed) == 0
