@@ -118,6 +118,10 @@ int rtb_render_pixels(rtb_scene* scene, const rtb_render_params* params, const u
  *     (HOST), computed by the same device code the trace kernel's epilogue uses. */
 int rtb_color_to_u8(rtb_scene* scene, const float* linear, uint64_t n, uint8_t* out);
 
+/* Raw device counters of the last render on this scene (16 values; diagnostics of the RTB_FLAG_COUNTERS build, layout in
+ * csrc/rtb_common.cuh). */
+int rtb_scene_get_counters(rtb_scene* scene, uint64_t* out16);
+
 /* Device self-test: the shared-reciprocal divisions of the trace kernels (csrc/rtb_trace.cu, div3_exact / div_by) against
  * the compiler's IEEE `/` on n pseudo-random operand sets; *mismatches must come back 0. */
 int rtb_selftest_division(rtb_scene* scene, uint64_t seed, uint64_t n, uint64_t* mismatches);

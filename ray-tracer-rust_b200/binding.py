@@ -47,7 +47,7 @@ class SceneInfo(C.Structure):
 
 
 EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_render",
-           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_import_obj",
+           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_import_obj",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
 
 _lib = None
@@ -72,6 +72,7 @@ def lib():
         L.rtb_color_to_u8.argtypes = [vp, vp, C.c_uint64, vp]
         L.rtb_scene_get_tie_ranks.argtypes = [vp, vp]
         L.rtb_scene_get_nodes.argtypes = [vp, vp]
+        L.rtb_scene_get_counters.argtypes = [vp, vp]
         L.rtb_selftest_division.argtypes = [vp, C.c_uint64, C.c_uint64, vp]
         L.rtb_owned_rows.argtypes = [C.c_uint32] * 4; L.rtb_owned_rows.restype = C.c_uint32
         L.rtb_deinterleave_bands.argtypes = [C.c_int32, vp, C.c_uint64, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]
@@ -225,6 +226,11 @@ class Scene:
         out = np.zeros((n, 16), np.float32)
         _check(lib().rtb_scene_get_nodes(self._h, _ptr(out)))
         return out, out[:, 12:14].copy().view(np.int32)
+
+    def counters(self):
+        out = np.zeros(16, np.uint64)
+        _check(lib().rtb_scene_get_counters(self._h, _ptr(out)))
+        return out
 
     def selftest_division(self, n=1 << 26, seed=1):
         """Mismatches between the kernels' shared-reciprocal division and IEEE `/` over n random operand sets (must be 0)."""

@@ -44,6 +44,7 @@ struct rtb_scene {
     uint16_t* d_light_perm; size_t light_perm_cap;
     float* d_light_gbox; size_t light_gbox_cap;
     float4* d_subitems; size_t sub_cap;
+    uint4* d_sublists; int* d_cand_pool; size_t pool_cap;
     unsigned long long* d_counters;
     float* d_light_box;                          // 6 floats, bounds of d_light_pts (k_light_bounds)
     uint8_t* d_frame; size_t frame_cap;          // staging for rtb_render (host output)
@@ -114,7 +115,7 @@ uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint
 void rtb_scene_destroy(rtb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm); cudaFree(s->d_light_gbox); cudaFree(s->d_subitems);
+    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm); cudaFree(s->d_light_gbox); cudaFree(s->d_subitems); cudaFree(s->d_sublists); cudaFree(s->d_cand_pool);
     cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame);
     cudaFree(s->d_records); cudaFree(s->d_items); cudaFree(s->d_masks); cudaFree(s->d_queue_ctl);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
@@ -153,7 +154,7 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     TRY_(cudaEventCreate(&s->evk[0])); TRY_(cudaEventCreate(&s->evk[1]));
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
-    TRY_(cudaMalloc(&s->d_queue_ctl, 8 * sizeof(uint32_t)));
+    TRY_(cudaMalloc(&s->d_queue_ctl, 16 * sizeof(uint32_t)));
     if (n) {
         TRY_(cudaMalloc(&d_verts, (size_t)n * 9 * 4)); TRY_(cudaMalloc(&d_colors, (size_t)n * 3 * 4));
         TRY_(cudaMemcpyAsync(d_verts, desc->verts, (size_t)n * 9 * 4, cudaMemcpyHostToDevice, s->stream));
@@ -281,9 +282,19 @@ static int prepare_wavefront(rtb_scene* s, cudaStream_t st, TraceArgs* a) {
     }
     const uint64_t sub_need = rays * a->n_groups;
     if (sub_need > s->sub_cap) {
-        cudaFree(s->d_subitems); s->d_subitems = nullptr; s->sub_cap = 0;
+        cudaFree(s->d_subitems); cudaFree(s->d_sublists); s->d_subitems = nullptr; s->d_sublists = nullptr; s->sub_cap = 0;
         CUDA_TRY(cudaMalloc(&s->d_subitems, (sub_need ? sub_need : 1) * RTB_SUB_F4 * sizeof(float4)));
+        CUDA_TRY(cudaMalloc(&s->d_sublists, (sub_need ? sub_need : 1) * sizeof(uint4)));
         s->sub_cap = sub_need;
+    }
+    // candidate pool: 16 entries per ray on average is far above anything measured (big_bunny: 2.4); a full pool is not
+    // an error, the remaining pairs walk the BVH instead
+    uint64_t pool_need = rays * 16;
+    if (pool_need > 0xfffffff0ull) pool_need = 0xfffffff0ull;
+    if (pool_need > s->pool_cap) {
+        cudaFree(s->d_cand_pool); s->d_cand_pool = nullptr; s->pool_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_cand_pool, (pool_need ? pool_need : 1) * sizeof(int)));
+        s->pool_cap = pool_need;
     }
     const uint64_t mask_need = rays * a->mask_words;
     if (mask_need > s->mask_cap) {
@@ -291,8 +302,9 @@ static int prepare_wavefront(rtb_scene* s, cudaStream_t st, TraceArgs* a) {
         CUDA_TRY(cudaMalloc(&s->d_masks, (mask_need ? mask_need : 1) * sizeof(uint32_t)));
         s->mask_cap = mask_need;
     }
-    CUDA_TRY(cudaMemsetAsync(s->d_queue_ctl, 0, 8 * sizeof(uint32_t), st));
+    CUDA_TRY(cudaMemsetAsync(s->d_queue_ctl, 0, 16 * sizeof(uint32_t), st));
     a->records = s->d_records; a->items = s->d_items; a->masks = s->d_masks; a->queue_ctl = s->d_queue_ctl; a->subitems = s->d_subitems;
+    a->sublists = s->d_sublists; a->cand_pool = s->d_cand_pool; a->pool_cap = (uint32_t)s->pool_cap;
     a->queue_ticket = (unsigned long long*)(s->d_queue_ctl + 2);
     return RTB_OK;
 }
@@ -303,7 +315,7 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
     CUDA_TRY(cudaMemcpyAsync(h, s->d_counters, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     if (h[RTB_CTR_OVERFLOW]) return fail(RTB_ERR_LIMIT, "traversal stack overflow");
-    if (launches >= 7) {
+    if (launches >= 8) {
         CUDA_TRY(cudaEventElapsedTime(&k_ms[0], s->ev0, s->evk[0]));
         CUDA_TRY(cudaEventElapsedTime(&k_ms[1], s->evk[0], s->evk[1]));
         CUDA_TRY(cudaEventElapsedTime(&k_ms[2], s->evk[1], s->ev1));
@@ -314,11 +326,11 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
         st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
         st->kernel_ms = ms; st->launches = launches;
         st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];
-        unsigned int qc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        unsigned int qc[16] = {0};
         CUDA_TRY(cudaMemcpy(qc, s->d_queue_ctl, sizeof(qc), cudaMemcpyDeviceToHost));
-        st->queued_hits = launches >= 7 ? qc[0] : 0;
-        st->queued_walks = launches >= 7 ? qc[5] : 0;
-        st->queued_groups = launches >= 7 ? qc[4] : 0;
+        st->queued_hits = launches >= 8 ? qc[0] : 0;
+        st->queued_walks = launches >= 8 ? qc[4] : 0;
+        st->queued_groups = launches >= 8 ? qc[4] + qc[6] : 0;
     }
     return RTB_OK;
 }
@@ -359,7 +371,7 @@ int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stat
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     float ms = 0.0f;
     CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 7, stats);
+    return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 8, stats);
 }
 
 int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* pixels, uint64_t n_pix, float* rgb_lin,
@@ -398,7 +410,7 @@ int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* 
     }
     TRY_(cudaStreamSynchronize(s->stream));
     TRY_(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    rc = fetch_stats(s, p, n_pix, ms, n_pix ? 7 : 3, stats);
+    rc = fetch_stats(s, p, n_pix, ms, n_pix ? 8 : 3, stats);
 cleanup:
     cudaFree(d_pix); cudaFree(d_lin); cudaFree(d_rgb8); cudaFree(d_hc); cudaFree(d_p0); cudaFree(d_t0);
     return rc;
@@ -443,6 +455,13 @@ int rtb_scene_get_tie_ranks(rtb_scene* s, int32_t* out) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
     cudaFree(d);
     if (e != cudaSuccess) return fail(RTB_ERR_CUDA, "rtb_scene_get_tie_ranks: %s", cudaGetErrorString(e));
+    return RTB_OK;
+}
+
+int rtb_scene_get_counters(rtb_scene* s, uint64_t* out16) {
+    if (!s || !out16) return fail(RTB_ERR_ARG, "rtb_scene_get_counters: null argument");
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaMemcpy(out16, s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     return RTB_OK;
 }
 

@@ -62,9 +62,13 @@ struct TraceArgs {
     // wavefront buffers (rtb_trace.cu): hit records [nb_ray][n_pix_padded], shadow queue, occlusion masks
     uint2* records;                      // {t bits, prim | flags} per (ray r, padded pixel)
     float4* items;                       // RTB_ITEM_F4 float4 per queued hit point
-    float4* subitems;                    // RTB_SUB_F4 float4 per (queued hit point, light-sample group) that can be occluded
+    float4* subitems;                    // RTB_SUB_F4 float4 per (hit point, light-sample group) pair that walks the BVH per ray
+    uint4* sublists;                     // {hit slot, group, pool offset, n} per pair with a complete candidate list
+    int* cand_pool;                      // candidate primitives of the list pairs (bump-allocated by k_shadow_plan)
+    uint32_t pool_cap;
     uint32_t* masks;                     // mask_words per queued hit point: bit i = light sample i occluded
-    uint32_t* queue_ctl;                 // [0] hit points queued by k_primary [1] k_shadow_plan ticket [4] sub-items [5] of which need a BVH walk
+    uint32_t* queue_ctl;                 // [0] hit points queued by k_primary [1] k_shadow_plan ticket [2,3] k_shadow_queue ticket [4] walk pairs
+                                         // [5] of which with an entry node [6] list pairs [7] pool entries used [8,9] k_shadow_lists ticket
     unsigned long long* queue_ticket;    // (= queue_ctl + 2) next unclaimed ray of k_shadow_queue
     uint32_t n_pix_padded, tiles_x, mask_words;
     // outputs
@@ -81,4 +85,4 @@ struct TraceArgs {
 #define RTB_CTR_BOX 3
 #define RTB_CTR_TRI 4
 #define RTB_CTR_OVERFLOW 5
-#define RTB_NUM_CTRS 8
+#define RTB_NUM_CTRS 16   // 6.. : diagnostics of the counters build (k_shadow_queue: node steps of occluded / free rays, occluded rays)

@@ -55,6 +55,7 @@ extern "C" {
                              rgb_lin: *mut f32, rgb8: *mut u8, hit_count: *mut u8, prim0: *mut i32, t0: *mut f32,
                              stats: *mut RtbStats) -> i32;
     pub fn rtb_color_to_u8(scene: *mut RtbScene, linear: *const f32, n: u64, out: *mut u8) -> i32;
+    pub fn rtb_scene_get_counters(scene: *mut RtbScene, out16: *mut u64) -> i32;
     pub fn rtb_selftest_division(scene: *mut RtbScene, seed: u64, n: u64, mismatches: *mut u64) -> i32;
     pub fn rtb_scene_get_tie_ranks(scene: *mut RtbScene, out: *mut i32) -> i32;
     pub fn rtb_scene_get_nodes(scene: *mut RtbScene, out: *mut f32) -> i32;
