@@ -43,7 +43,7 @@ struct rtb_scene {
     float4* d_light_pts; uint32_t light_pts_cap;
     uint16_t* d_light_perm; size_t light_perm_cap;
     float* d_light_gbox; size_t light_gbox_cap;
-    float4* d_subitems; size_t sub_cap;
+    uint4* d_subitems; size_t sub_cap;
     uint4* d_sublists; int* d_cand_pool; size_t pool_cap;
     unsigned long long* d_counters;
     float* d_light_box;                          // 6 floats, bounds of d_light_pts (k_light_bounds)
@@ -54,7 +54,9 @@ struct rtb_scene {
     uint8_t* h_pinned; size_t pinned_cap;
     cudaStream_t stream;
     cudaEvent_t ev0, ev1;
-    cudaEvent_t evk[2];                          // between the wavefront kernels (per-kernel times in rtb_stats)
+    cudaEvent_t evp[4 * 32];                     // per-chunk events around the wavefront kernels (per-kernel times in rtb_stats)
+    uint32_t timed_chunks, n_chunks;
+    uint64_t chunk_rays;                         // rays per wavefront chunk (RTB200_CHUNK_RAYS, default 16 Mi)
 };
 
 // ---- Color::to_rgba threshold table (color.rs:10-33) ---------------------------------------
@@ -121,7 +123,7 @@ void rtb_scene_destroy(rtb_scene* s) {
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
-    for (int k = 0; k < 2; ++k) if (s->evk[k]) cudaEventDestroy(s->evk[k]);
+    for (int k = 0; k < 4 * 32; ++k) if (s->evp[k]) cudaEventDestroy(s->evp[k]);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -151,7 +153,9 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
 #define TRY_(x) do { e = (x); if (e != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e)); goto cleanup; } } while (0)
     TRY_(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     TRY_(cudaEventCreate(&s->ev0)); TRY_(cudaEventCreate(&s->ev1));
-    TRY_(cudaEventCreate(&s->evk[0])); TRY_(cudaEventCreate(&s->evk[1]));
+    for (int k = 0; k < 4 * 32; ++k) TRY_(cudaEventCreate(&s->evp[k]));
+    s->chunk_rays = 16ull << 20;
+    if (const char* env = getenv("RTB200_CHUNK_RAYS")) { const long long v = atoll(env); if (v > 0) s->chunk_rays = (uint64_t)v; }
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
     TRY_(cudaMalloc(&s->d_queue_ctl, 16 * sizeof(uint32_t)));
@@ -223,7 +227,10 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     }
     CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
     // light-sample groups (k_light_groups): at most RTB_MAX_GROUPS runs of the Hilbert-sorted samples, ~32 samples each
-    uint32_t n_groups = (p->nb_light_sample + 31) / 32;
+#ifndef RTB_GROUP_TARGET
+#define RTB_GROUP_TARGET 32
+#endif
+    uint32_t n_groups = (p->nb_light_sample + RTB_GROUP_TARGET - 1) / RTB_GROUP_TARGET;
     if (n_groups > RTB_MAX_GROUPS) n_groups = RTB_MAX_GROUPS;
     if (n_groups == 0) n_groups = 1;
     uint32_t group_size = (p->nb_light_sample + n_groups - 1) / n_groups;
@@ -258,32 +265,21 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     return RTB_OK;
 }
 
-// Sizes the wavefront buffers for n_pix_padded pixels x nb_ray rays (worst case: every ray hits and is queued) and
-// resets the queue.  Frame mode: a.pixel_list == nullptr, tiles of 8x4 pixels; list mode: a.n_pix listed pixels.
-static int prepare_wavefront(rtb_scene* s, cudaStream_t st, TraceArgs* a) {
-    uint64_t npp;
-    if (a->pixel_list) {
-        npp = (a->n_pix + 255) / 256 * 256;
-        a->tiles_x = 0;
-    } else {
-        a->tiles_x = (a->width + 7) / 8;
-        const uint64_t tiles = (uint64_t)a->tiles_x * ((a->owned_rows + 3) / 4);
-        npp = (tiles * 32 + 255) / 256 * 256;
-    }
-    const uint64_t rays = npp * a->nb_ray;
-    if (rays >= 0x7fffffffull) return fail(RTB_ERR_LIMIT, "render: %llu rays in one call exceed the 2^31 record index", (unsigned long long)rays);
-    a->n_pix_padded = (uint32_t)npp;
-    a->mask_words = (a->nb_light_sample + 31) / 32;
+#define RTB_MAX_TIMED_CHUNKS 32
+
+// Grows (never shrinks) the wavefront buffers of the scene to hold one chunk of `rays` rays: worst case every ray hits,
+// is queued and keeps all its light-sample groups.
+static int reserve_wavefront(rtb_scene* s, uint64_t rays, uint32_t n_groups, uint32_t mask_words) {
     if (rays > s->rays_cap) {
         cudaFree(s->d_records); cudaFree(s->d_items); s->d_records = nullptr; s->d_items = nullptr; s->rays_cap = 0;
         CUDA_TRY(cudaMalloc(&s->d_records, rays * sizeof(uint2)));
         CUDA_TRY(cudaMalloc(&s->d_items, rays * RTB_ITEM_F4 * sizeof(float4)));
         s->rays_cap = rays;
     }
-    const uint64_t sub_need = rays * a->n_groups;
+    const uint64_t sub_need = rays * n_groups;
     if (sub_need > s->sub_cap) {
         cudaFree(s->d_subitems); cudaFree(s->d_sublists); s->d_subitems = nullptr; s->d_sublists = nullptr; s->sub_cap = 0;
-        CUDA_TRY(cudaMalloc(&s->d_subitems, (sub_need ? sub_need : 1) * RTB_SUB_F4 * sizeof(float4)));
+        CUDA_TRY(cudaMalloc(&s->d_subitems, (sub_need ? sub_need : 1) * sizeof(uint4)));
         CUDA_TRY(cudaMalloc(&s->d_sublists, (sub_need ? sub_need : 1) * sizeof(uint4)));
         s->sub_cap = sub_need;
     }
@@ -296,16 +292,55 @@ static int prepare_wavefront(rtb_scene* s, cudaStream_t st, TraceArgs* a) {
         CUDA_TRY(cudaMalloc(&s->d_cand_pool, (pool_need ? pool_need : 1) * sizeof(int)));
         s->pool_cap = pool_need;
     }
-    const uint64_t mask_need = rays * a->mask_words;
+    const uint64_t mask_need = rays * mask_words;
     if (mask_need > s->mask_cap) {
         cudaFree(s->d_masks); s->d_masks = nullptr; s->mask_cap = 0;
         CUDA_TRY(cudaMalloc(&s->d_masks, (mask_need ? mask_need : 1) * sizeof(uint32_t)));
         s->mask_cap = mask_need;
     }
-    CUDA_TRY(cudaMemsetAsync(s->d_queue_ctl, 0, 16 * sizeof(uint32_t), st));
-    a->records = s->d_records; a->items = s->d_items; a->masks = s->d_masks; a->queue_ctl = s->d_queue_ctl; a->subitems = s->d_subitems;
-    a->sublists = s->d_sublists; a->cand_pool = s->d_cand_pool; a->pool_cap = (uint32_t)s->pool_cap;
-    a->queue_ticket = (unsigned long long*)(s->d_queue_ctl + 2);
+    return RTB_OK;
+}
+
+// Runs the wavefront kernels over the whole frame (a.pixel_list == nullptr: 8x4 pixel tiles of the owned rows) or pixel
+// list, in chunks of at most s->chunk_rays rays so that the intermediate buffers stay bounded (about 170 bytes per ray
+// in the worst case) whatever the resolution and rays per pixel.  A chunk is a whole number of tile rows (or of 256
+// listed pixels).  timed: record the per-kernel events of the first RTB_MAX_TIMED_CHUNKS chunks.
+static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st, bool timed) {
+    s->timed_chunks = 0; s->n_chunks = 0;
+    uint64_t unit, units_total;                       // pixels per granule, granules
+    if (a.pixel_list) {
+        unit = 256; units_total = (a.n_pix + 255) / 256; a.tiles_x = 0;
+    } else {
+        a.tiles_x = (a.width + 7) / 8;
+        unit = (uint64_t)a.tiles_x * 32; units_total = (a.owned_rows + 3) / 4;
+    }
+    if (units_total == 0) return RTB_OK;
+    const uint64_t per_pixel = a.nb_ray ? a.nb_ray : 1;
+    uint64_t units_per_chunk = s->chunk_rays / (unit * per_pixel);
+    if (units_per_chunk == 0) units_per_chunk = 1;
+    if (units_per_chunk > units_total) units_per_chunk = units_total;
+    const uint64_t npp_max = (units_per_chunk * unit + 255) / 256 * 256;
+    if (npp_max * per_pixel >= 0x7fffffffull)
+        return fail(RTB_ERR_LIMIT, "render: one tile row needs %llu rays, above the 2^31 record index", (unsigned long long)(npp_max * per_pixel));
+    a.mask_words = (a.nb_light_sample + 31) / 32;
+    int rc = reserve_wavefront(s, npp_max * per_pixel, a.n_groups, a.mask_words);
+    if (rc != RTB_OK) return rc;
+    a.records = s->d_records; a.items = s->d_items; a.masks = s->d_masks; a.queue_ctl = s->d_queue_ctl; a.subitems = s->d_subitems;
+    a.sublists = s->d_sublists; a.cand_pool = s->d_cand_pool; a.pool_cap = (uint32_t)s->pool_cap;
+    a.queue_ticket = (unsigned long long*)(s->d_queue_ctl + 2);
+    const uint64_t pix_total = a.pixel_list ? a.n_pix : units_total * unit;
+    for (uint64_t u0 = 0; u0 < units_total; u0 += units_per_chunk) {
+        const uint64_t nu = units_total - u0 < units_per_chunk ? units_total - u0 : units_per_chunk;
+        const uint64_t base = u0 * unit;
+        uint64_t n = nu * unit;
+        if (base + n > pix_total) n = pix_total - base;
+        a.pix_base = (uint32_t)base; a.n_pix_chunk = (uint32_t)n; a.n_pix_padded = (uint32_t)((nu * unit + 255) / 256 * 256);
+        CUDA_TRY(cudaMemsetAsync(s->d_queue_ctl, 0, 16 * sizeof(uint32_t), st));
+        cudaEvent_t* ev = nullptr;
+        if (timed && s->timed_chunks < RTB_MAX_TIMED_CHUNKS) ev = s->evp + 4 * s->timed_chunks++;
+        CUDA_TRY(rtb_launch_trace(a, count, st, ev));
+        s->n_chunks++;
+    }
     return RTB_OK;
 }
 
@@ -315,22 +350,22 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
     CUDA_TRY(cudaMemcpyAsync(h, s->d_counters, sizeof(h), cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     if (h[RTB_CTR_OVERFLOW]) return fail(RTB_ERR_LIMIT, "traversal stack overflow");
-    if (launches >= 8) {
-        CUDA_TRY(cudaEventElapsedTime(&k_ms[0], s->ev0, s->evk[0]));
-        CUDA_TRY(cudaEventElapsedTime(&k_ms[1], s->evk[0], s->evk[1]));
-        CUDA_TRY(cudaEventElapsedTime(&k_ms[2], s->evk[1], s->ev1));
+    for (uint32_t c = 0; c < s->timed_chunks; ++c) {
+        for (int k = 0; k < 3; ++k) {
+            float t = 0.0f;
+            CUDA_TRY(cudaEventElapsedTime(&t, s->evp[4 * c + k], s->evp[4 * c + k + 1]));
+            k_ms[k] += t;
+        }
     }
     if (st) {
         st->primary_rays = n_pix * p->nb_ray; st->primary_hits = h[RTB_CTR_PRIMARY_HITS];
         st->shadow_rays = h[RTB_CTR_SHADOW]; st->shadow_occluded = h[RTB_CTR_OCCLUDED];
         st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
-        st->kernel_ms = ms; st->launches = launches;
+        st->kernel_ms = ms;
+        st->launches = 3 + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? 3 : 0));   // light table, bounds, groups + per chunk
         st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];
-        unsigned int qc[16] = {0};
-        CUDA_TRY(cudaMemcpy(qc, s->d_queue_ctl, sizeof(qc), cudaMemcpyDeviceToHost));
-        st->queued_hits = launches >= 8 ? qc[0] : 0;
-        st->queued_walks = launches >= 8 ? qc[4] : 0;
-        st->queued_groups = launches >= 8 ? qc[4] + qc[6] : 0;
+        st->queued_hits = (uint32_t)h[RTB_CTR_QUEUED]; st->queued_groups = (uint32_t)h[RTB_CTR_PAIRS];
+        st->queued_walks = (uint32_t)h[RTB_CTR_WALKS];
     }
     return RTB_OK;
 }
@@ -344,10 +379,7 @@ int rtb_render_device(rtb_scene* s, const rtb_render_params* p, void* d_rgb8, vo
     if (rc != RTB_OK) return rc;
     if (!d_rgb8) return fail(RTB_ERR_ARG, "rtb_render_device: null output");
     a.rgb8 = (uint8_t*)d_rgb8;
-    rc = prepare_wavefront(s, st, &a);
-    if (rc != RTB_OK) return rc;
-    CUDA_TRY(rtb_launch_trace(a, (p->flags & RTB_FLAG_COUNTERS) != 0, st, nullptr));
-    return RTB_OK;
+    return run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, st, false);
 }
 
 int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stats* stats) {
@@ -362,10 +394,9 @@ int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stat
         s->frame_cap = bytes;
     }
     a.rgb8 = s->d_frame;
-    rc = prepare_wavefront(s, s->stream, &a);
-    if (rc != RTB_OK) return rc;
     CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
-    CUDA_TRY(rtb_launch_trace(a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, s->evk));
+    rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, true);
+    if (rc != RTB_OK) return rc;
     CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
     if (bytes) CUDA_TRY(cudaMemcpyAsync(rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
@@ -394,12 +425,12 @@ int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* 
         if (t0) TRY_(cudaMalloc(&d_t0, n_pix * 4));
     }
     a.pixel_list = d_pix; a.n_pix = n_pix; a.out_rgb_lin = d_lin; a.rgb8 = d_rgb8; a.out_hit_count = d_hc; a.out_prim0 = d_p0; a.out_t0 = d_t0;
+    s->timed_chunks = 0; s->n_chunks = 0;
+    TRY_(cudaEventRecord(s->ev0, s->stream));
     if (n_pix) {
-        rc = prepare_wavefront(s, s->stream, &a);
+        rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, true);
         if (rc != RTB_OK) goto cleanup;
     }
-    TRY_(cudaEventRecord(s->ev0, s->stream));
-    if (n_pix) TRY_(rtb_launch_trace(a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, s->evk));
     TRY_(cudaEventRecord(s->ev1, s->stream));
     if (n_pix) {
         if (rgb_lin) TRY_(cudaMemcpyAsync(rgb_lin, d_lin, n_pix * 12, cudaMemcpyDeviceToHost, s->stream));

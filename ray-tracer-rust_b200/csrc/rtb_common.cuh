@@ -16,8 +16,7 @@
 #define RTB_MAX_CAND 8             // primitives a hit point's shadow rays test directly (multiple of 4)
 #endif
 #define RTB_ITEM_F4 2                        // float4 per queued hit point: {ray id, prim word, -, -} {p_hit}
-#define RTB_SUB_F4 (1 + RTB_MAX_CAND / 4)    // float4 per shadow sub-item: {hit slot, group, entry, n_cand} {cand...}
-#define RTB_MAX_GROUPS 8                     // light-sample groups per hit point (k_light_groups)
+#define RTB_MAX_GROUPS 16                    // light-sample groups per hit point (k_light_groups)
 
 struct f3 { float x, y, z; };
 
@@ -62,7 +61,7 @@ struct TraceArgs {
     // wavefront buffers (rtb_trace.cu): hit records [nb_ray][n_pix_padded], shadow queue, occlusion masks
     uint2* records;                      // {t bits, prim | flags} per (ray r, padded pixel)
     float4* items;                       // RTB_ITEM_F4 float4 per queued hit point
-    float4* subitems;                    // RTB_SUB_F4 float4 per (hit point, light-sample group) pair that walks the BVH per ray
+    uint4* subitems;                     // {hit slot, group, entry node, -} per (hit point, light-sample group) pair that walks the BVH per ray
     uint4* sublists;                     // {hit slot, group, pool offset, n} per pair with a complete candidate list
     int* cand_pool;                      // candidate primitives of the list pairs (bump-allocated by k_shadow_plan)
     uint32_t pool_cap;
@@ -70,7 +69,8 @@ struct TraceArgs {
     uint32_t* queue_ctl;                 // [0] hit points queued by k_primary [1] k_shadow_plan ticket [2,3] k_shadow_queue ticket [4] walk pairs
                                          // [5] of which with an entry node [6] list pairs [7] pool entries used [8,9] k_shadow_lists ticket
     unsigned long long* queue_ticket;    // (= queue_ctl + 2) next unclaimed ray of k_shadow_queue
-    uint32_t n_pix_padded, tiles_x, mask_words;
+    uint32_t n_pix_padded, tiles_x, mask_words;   // n_pix_padded: record stride of THIS chunk (multiple of 256)
+    uint32_t pix_base, n_pix_chunk;      // chunk = padded pixel indices [pix_base, pix_base + n_pix_chunk)
     // outputs
     uint8_t* rgb8;                       // frame mode: owned rows, compact; list mode: 3 bytes per listed pixel
     const uint2* pixel_list;             // list mode (else nullptr)
@@ -85,4 +85,7 @@ struct TraceArgs {
 #define RTB_CTR_BOX 3
 #define RTB_CTR_TRI 4
 #define RTB_CTR_OVERFLOW 5
-#define RTB_NUM_CTRS 16   // 6.. : diagnostics of the counters build (k_shadow_queue: node steps of occluded / free rays, occluded rays)
+#define RTB_NUM_CTRS 16   // 6..8: diagnostics of the counters build (k_shadow_queue: node steps of occluded / free rays, occluded rays)
+#define RTB_CTR_QUEUED 9        // summed over the chunks of a call by k_shade: queued hit points, (hit point, group) pairs, walk pairs
+#define RTB_CTR_PAIRS 10
+#define RTB_CTR_WALKS 11

@@ -259,3 +259,25 @@ def test_shared_reciprocal_division_is_ieee(gpu_big_bunny):
     with exponents on both sides of the fast-path range and extreme mantissas."""
     for seed in (1, 2):
         assert gpu_big_bunny.selftest_division(1 << 27, seed) == 0
+
+
+def test_chunked_wavefront_equals_single_pass(rtb, big_bunny_inputs, monkeypatch):
+    """The frame is rendered in chunks of RTB200_CHUNK_RAYS rays (bounded intermediate buffers); tiny chunks must give the
+    same bytes and statistics as one pass, for frames and for pixel lists."""
+    v, c, smp = big_bunny_inputs
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=2, nb_light_sample=40)
+    ref_sc = rtb.Scene(v, c); ref_sc.set_samples(smp)
+    ref, st_ref = ref_sc.render(**kw)
+    pix = S.stratified_pixels(640, 360, 7, seed=2)
+    ref_list = ref_sc.render_pixels(pix, **kw)
+    assert st_ref["launches"] == 3 + 5
+    monkeypatch.setenv("RTB200_CHUNK_RAYS", "30000")
+    sc = rtb.Scene(v, c); sc.set_samples(smp)
+    got, st = sc.render(**kw)
+    assert (got == ref).all()
+    assert st["launches"] > 3 + 5 * 10
+    for k in ("primary_hits", "shadow_rays", "shadow_occluded", "queued_hits", "queued_groups"):
+        assert st[k] == st_ref[k], k
+    got_list = sc.render_pixels(pix, **kw)
+    for k in ("rgb_lin", "rgb8", "hit_count", "prim0", "t0"):
+        assert (got_list[k] == ref_list[k]).all(), k
