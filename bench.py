@@ -208,7 +208,7 @@ def main():
     for _ in range(3):
         flush_buf.zero_()
         torch.cuda.synchronize(dev)
-        _, s1 = scene.render(width=WIDTH, height=HEIGHT, band_rows=BAND_ROWS, rank=rank, world=world, **kw)
+        _, s1 = scene.render(width=WIDTH, height=HEIGHT, band_rows=BAND_ROWS, rank=rank, world=world, profile=True, **kw)
         kms.append(s1["kernel_ms"])
         per_kernel["k_primary"].append(s1["primary_ms"])
         per_kernel["k_shadow_plan+k_shadow_queue"].append(s1["shadow_ms"])

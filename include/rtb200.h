@@ -65,13 +65,16 @@ typedef struct {
 } rtb_render_params;
 
 #define RTB_FLAG_COUNTERS 1u      /* also count AABB / triangle tests (slower instrumented kernel) */
+#define RTB_FLAG_PROFILE 2u       /* per-kernel times in rtb_stats: the chunks of the frame run one after the other on one stream
+                                     instead of overlapping on two (a little slower) */
 
 typedef struct {
     uint64_t primary_rays, primary_hits, shadow_rays, shadow_occluded;
     uint64_t box_tests, tri_tests;   /* only with RTB_FLAG_COUNTERS, else 0 */
     float kernel_ms;                 /* device time of the trace kernels of this call (CUDA events) */
     uint32_t launches;               /* kernels launched by this call */
-    float primary_ms, shadow_ms, shade_ms;   /* k_primary / k_shadow_plan + k_shadow_queue / k_shade, same events */
+    float primary_ms, shadow_ms, shade_ms;   /* k_primary / k_shadow_plan + k_shadow_lists + k_shadow_queue / k_shade; only with
+                                                RTB_FLAG_PROFILE, else 0 */
     uint32_t queued_hits;            /* hit points whose shadow rays needed the BVH (shadow queue length) */
     uint32_t queued_groups;          /* (hit point, light-sample group) pairs left after the per-group bundle test */
     uint32_t queued_walks;           /* ... of which need a per-ray BVH walk (not just a short candidate list) */

@@ -14,6 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(_HERE, "librtb200.so")   # override: kernel-variant experiments
 
 RTB_FLAG_COUNTERS = 1
+RTB_FLAG_PROFILE = 2
 
 
 class RtbError(RuntimeError):
@@ -194,13 +195,13 @@ class Scene:
     @staticmethod
     def params(width=1920, height=1080, nb_ray=1, nb_light_sample=100, eye=DEFAULT_CAMERA["eye"],
                look_at=DEFAULT_CAMERA["look_at"], up=DEFAULT_CAMERA["up"], distance=DEFAULT_CAMERA["distance"],
-               band_rows=8, rank=0, world=1, counters=False):
+               band_rows=8, rank=0, world=1, counters=False, profile=False):
         p = RenderParams()
         p.width, p.height, p.nb_ray, p.nb_light_sample = width, height, nb_ray, nb_light_sample
         p.eye[:] = [float(x) for x in eye]; p.look_at[:] = [float(x) for x in look_at]; p.up[:] = [float(x) for x in up]
         p.distance = float(distance)
         p.band_rows, p.rank, p.world = band_rows, rank, world
-        p.flags = RTB_FLAG_COUNTERS if counters else 0
+        p.flags = (RTB_FLAG_COUNTERS if counters else 0) | (RTB_FLAG_PROFILE if profile else 0)
         return p
 
     def render(self, out=None, **kw):

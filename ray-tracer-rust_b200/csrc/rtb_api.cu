@@ -43,14 +43,18 @@ struct rtb_scene {
     float4* d_light_pts; uint32_t light_pts_cap;
     uint16_t* d_light_perm; size_t light_perm_cap;
     float* d_light_gbox; size_t light_gbox_cap;
-    uint4* d_subitems; size_t sub_cap;
-    uint4* d_sublists; int* d_cand_pool; size_t pool_cap;
     unsigned long long* d_counters;
     float* d_light_box;                          // 6 floats, bounds of d_light_pts (k_light_bounds)
     uint8_t* d_frame; size_t frame_cap;          // staging for rtb_render (host output)
     // wavefront buffers, grown on demand and kept (see rtb_trace.cu)
-    uint2* d_records; float4* d_items; uint32_t* d_masks; uint32_t* d_queue_ctl;
-    size_t rays_cap, mask_cap;
+    // (two sets: consecutive chunks run on two worker streams so that one chunk's kernel tails overlap the other's work)
+    struct WaveBufs {
+        uint2* d_records; float4* d_items; uint32_t* d_masks; uint32_t* d_queue_ctl;
+        uint4* d_subitems; uint4* d_sublists; int* d_cand_pool;
+        size_t rays_cap, mask_cap, sub_cap, pool_cap;
+    } wb[2];
+    cudaStream_t wstream[2];
+    cudaEvent_t ev_fork, ev_join[2];
     uint8_t* h_pinned; size_t pinned_cap;
     cudaStream_t stream;
     cudaEvent_t ev0, ev1;
@@ -117,9 +121,16 @@ uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint
 void rtb_scene_destroy(rtb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm); cudaFree(s->d_light_gbox); cudaFree(s->d_subitems); cudaFree(s->d_sublists); cudaFree(s->d_cand_pool);
+    cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm); cudaFree(s->d_light_gbox);
     cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame);
-    cudaFree(s->d_records); cudaFree(s->d_items); cudaFree(s->d_masks); cudaFree(s->d_queue_ctl);
+    for (int k = 0; k < 2; ++k) {
+        rtb_scene::WaveBufs& b = s->wb[k];
+        cudaFree(b.d_records); cudaFree(b.d_items); cudaFree(b.d_masks); cudaFree(b.d_queue_ctl);
+        cudaFree(b.d_subitems); cudaFree(b.d_sublists); cudaFree(b.d_cand_pool);
+        if (s->wstream[k]) cudaStreamDestroy(s->wstream[k]);
+        if (s->ev_join[k]) cudaEventDestroy(s->ev_join[k]);
+    }
+    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -158,7 +169,12 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     if (const char* env = getenv("RTB200_CHUNK_RAYS")) { const long long v = atoll(env); if (v > 0) s->chunk_rays = (uint64_t)v; }
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
-    TRY_(cudaMalloc(&s->d_queue_ctl, 16 * sizeof(uint32_t)));
+    for (int k = 0; k < 2; ++k) {
+        TRY_(cudaMalloc(&s->wb[k].d_queue_ctl, 16 * sizeof(uint32_t)));
+        TRY_(cudaStreamCreateWithFlags(&s->wstream[k], cudaStreamNonBlocking));
+        TRY_(cudaEventCreateWithFlags(&s->ev_join[k], cudaEventDisableTiming));
+    }
+    TRY_(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
     if (n) {
         TRY_(cudaMalloc(&d_verts, (size_t)n * 9 * 4)); TRY_(cudaMalloc(&d_colors, (size_t)n * 3 * 4));
         TRY_(cudaMemcpyAsync(d_verts, desc->verts, (size_t)n * 9 * 4, cudaMemcpyHostToDevice, s->stream));
@@ -269,34 +285,34 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
 
 // Grows (never shrinks) the wavefront buffers of the scene to hold one chunk of `rays` rays: worst case every ray hits,
 // is queued and keeps all its light-sample groups.
-static int reserve_wavefront(rtb_scene* s, uint64_t rays, uint32_t n_groups, uint32_t mask_words) {
-    if (rays > s->rays_cap) {
-        cudaFree(s->d_records); cudaFree(s->d_items); s->d_records = nullptr; s->d_items = nullptr; s->rays_cap = 0;
-        CUDA_TRY(cudaMalloc(&s->d_records, rays * sizeof(uint2)));
-        CUDA_TRY(cudaMalloc(&s->d_items, rays * RTB_ITEM_F4 * sizeof(float4)));
-        s->rays_cap = rays;
+static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_groups, uint32_t mask_words) {
+    if (rays > b.rays_cap) {
+        cudaFree(b.d_records); cudaFree(b.d_items); b.d_records = nullptr; b.d_items = nullptr; b.rays_cap = 0;
+        CUDA_TRY(cudaMalloc(&b.d_records, rays * sizeof(uint2)));
+        CUDA_TRY(cudaMalloc(&b.d_items, rays * RTB_ITEM_F4 * sizeof(float4)));
+        b.rays_cap = rays;
     }
     const uint64_t sub_need = rays * n_groups;
-    if (sub_need > s->sub_cap) {
-        cudaFree(s->d_subitems); cudaFree(s->d_sublists); s->d_subitems = nullptr; s->d_sublists = nullptr; s->sub_cap = 0;
-        CUDA_TRY(cudaMalloc(&s->d_subitems, (sub_need ? sub_need : 1) * sizeof(uint4)));
-        CUDA_TRY(cudaMalloc(&s->d_sublists, (sub_need ? sub_need : 1) * sizeof(uint4)));
-        s->sub_cap = sub_need;
+    if (sub_need > b.sub_cap) {
+        cudaFree(b.d_subitems); cudaFree(b.d_sublists); b.d_subitems = nullptr; b.d_sublists = nullptr; b.sub_cap = 0;
+        CUDA_TRY(cudaMalloc(&b.d_subitems, (sub_need ? sub_need : 1) * sizeof(uint4)));
+        CUDA_TRY(cudaMalloc(&b.d_sublists, (sub_need ? sub_need : 1) * sizeof(uint4)));
+        b.sub_cap = sub_need;
     }
     // candidate pool: 16 entries per ray on average is far above anything measured (big_bunny: 2.4); a full pool is not
     // an error, the remaining pairs walk the BVH instead
     uint64_t pool_need = rays * 16;
     if (pool_need > 0xfffffff0ull) pool_need = 0xfffffff0ull;
-    if (pool_need > s->pool_cap) {
-        cudaFree(s->d_cand_pool); s->d_cand_pool = nullptr; s->pool_cap = 0;
-        CUDA_TRY(cudaMalloc(&s->d_cand_pool, (pool_need ? pool_need : 1) * sizeof(int)));
-        s->pool_cap = pool_need;
+    if (pool_need > b.pool_cap) {
+        cudaFree(b.d_cand_pool); b.d_cand_pool = nullptr; b.pool_cap = 0;
+        CUDA_TRY(cudaMalloc(&b.d_cand_pool, (pool_need ? pool_need : 1) * sizeof(int)));
+        b.pool_cap = pool_need;
     }
     const uint64_t mask_need = rays * mask_words;
-    if (mask_need > s->mask_cap) {
-        cudaFree(s->d_masks); s->d_masks = nullptr; s->mask_cap = 0;
-        CUDA_TRY(cudaMalloc(&s->d_masks, (mask_need ? mask_need : 1) * sizeof(uint32_t)));
-        s->mask_cap = mask_need;
+    if (mask_need > b.mask_cap) {
+        cudaFree(b.d_masks); b.d_masks = nullptr; b.mask_cap = 0;
+        CUDA_TRY(cudaMalloc(&b.d_masks, (mask_need ? mask_need : 1) * sizeof(uint32_t)));
+        b.mask_cap = mask_need;
     }
     return RTB_OK;
 }
@@ -323,23 +339,42 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
     if (npp_max * per_pixel >= 0x7fffffffull)
         return fail(RTB_ERR_LIMIT, "render: one tile row needs %llu rays, above the 2^31 record index", (unsigned long long)(npp_max * per_pixel));
     a.mask_words = (a.nb_light_sample + 31) / 32;
-    int rc = reserve_wavefront(s, npp_max * per_pixel, a.n_groups, a.mask_words);
-    if (rc != RTB_OK) return rc;
-    a.records = s->d_records; a.items = s->d_items; a.masks = s->d_masks; a.queue_ctl = s->d_queue_ctl; a.subitems = s->d_subitems;
-    a.sublists = s->d_sublists; a.cand_pool = s->d_cand_pool; a.pool_cap = (uint32_t)s->pool_cap;
-    a.queue_ticket = (unsigned long long*)(s->d_queue_ctl + 2);
+    const uint64_t n_chunks = (units_total + units_per_chunk - 1) / units_per_chunk;
+    // timed (per-kernel events) or a single chunk: everything on the caller's stream with buffer set 0.  Otherwise chunk c
+    // runs on worker stream c & 1 with buffer set c & 1; the workers start after the caller's stream and it waits for them.
+    const bool overlap = !timed && n_chunks > 1;
+    for (int k = 0; k < (overlap ? 2 : 1); ++k) {
+        const int rc = reserve_wavefront(s->wb[k], npp_max * per_pixel, a.n_groups, a.mask_words);
+        if (rc != RTB_OK) return rc;
+    }
+    if (overlap) {
+        CUDA_TRY(cudaEventRecord(s->ev_fork, st));
+        for (int k = 0; k < 2; ++k) CUDA_TRY(cudaStreamWaitEvent(s->wstream[k], s->ev_fork, 0));
+    }
     const uint64_t pix_total = a.pixel_list ? a.n_pix : units_total * unit;
     for (uint64_t u0 = 0; u0 < units_total; u0 += units_per_chunk) {
+        const int k = overlap ? (int)(s->n_chunks & 1) : 0;
+        const rtb_scene::WaveBufs& b = s->wb[k];
+        cudaStream_t cs = overlap ? s->wstream[k] : st;
+        a.records = b.d_records; a.items = b.d_items; a.masks = b.d_masks; a.queue_ctl = b.d_queue_ctl; a.subitems = b.d_subitems;
+        a.sublists = b.d_sublists; a.cand_pool = b.d_cand_pool; a.pool_cap = (uint32_t)b.pool_cap;
+        a.queue_ticket = (unsigned long long*)(b.d_queue_ctl + 2);
         const uint64_t nu = units_total - u0 < units_per_chunk ? units_total - u0 : units_per_chunk;
         const uint64_t base = u0 * unit;
         uint64_t n = nu * unit;
         if (base + n > pix_total) n = pix_total - base;
         a.pix_base = (uint32_t)base; a.n_pix_chunk = (uint32_t)n; a.n_pix_padded = (uint32_t)((nu * unit + 255) / 256 * 256);
-        CUDA_TRY(cudaMemsetAsync(s->d_queue_ctl, 0, 16 * sizeof(uint32_t), st));
+        CUDA_TRY(cudaMemsetAsync(b.d_queue_ctl, 0, 16 * sizeof(uint32_t), cs));
         cudaEvent_t* ev = nullptr;
         if (timed && s->timed_chunks < RTB_MAX_TIMED_CHUNKS) ev = s->evp + 4 * s->timed_chunks++;
-        CUDA_TRY(rtb_launch_trace(a, count, st, ev));
+        CUDA_TRY(rtb_launch_trace(a, count, cs, ev));
         s->n_chunks++;
+    }
+    if (overlap) {
+        for (int k = 0; k < 2; ++k) {
+            CUDA_TRY(cudaEventRecord(s->ev_join[k], s->wstream[k]));
+            CUDA_TRY(cudaStreamWaitEvent(st, s->ev_join[k], 0));
+        }
     }
     return RTB_OK;
 }
@@ -395,7 +430,7 @@ int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stat
     }
     a.rgb8 = s->d_frame;
     CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
-    rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, true);
+    rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0);
     if (rc != RTB_OK) return rc;
     CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
     if (bytes) CUDA_TRY(cudaMemcpyAsync(rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
@@ -428,7 +463,7 @@ int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* 
     s->timed_chunks = 0; s->n_chunks = 0;
     TRY_(cudaEventRecord(s->ev0, s->stream));
     if (n_pix) {
-        rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, true);
+        rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0);
         if (rc != RTB_OK) goto cleanup;
     }
     TRY_(cudaEventRecord(s->ev1, s->stream));

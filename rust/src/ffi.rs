@@ -6,6 +6,7 @@ use std::os::raw::{c_char, c_void};
 
 pub const RTB_OK: i32 = 0;
 pub const RTB_FLAG_COUNTERS: u32 = 1;
+pub const RTB_FLAG_PROFILE: u32 = 2;
 
 #[repr(C)]
 pub struct RtbScene { _private: [u8; 0] }

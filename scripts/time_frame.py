@@ -19,9 +19,11 @@ if "nocheck" not in sys.argv:
     bad = int((g["rgb_lin"].view(np.uint32) != o["rgb_lin"].view(np.uint32)).sum() + (g["prim0"] != o["prim0"]).sum())
     print(tag, "parity mismatches:", bad, "of", len(pix), flush=True)
 for (w, h, nr) in ((1920, 1080, 1), (3840, 2160, 16)):
-    best = None
+    best = None; fast = 1e9
     for it in range(4):
-        img, st = sc.render(width=w, height=h, nb_ray=nr)
+        img, st = sc.render(width=w, height=h, nb_ray=nr, profile=True)
         if best is None or st["kernel_ms"] < best["kernel_ms"]: best = st
-    print("%s %dx%d spp%d: total %.2f ms  primary %.2f  shadow %.2f  shade %.2f  queued %d hits -> %d sub-items (%d walks) of %d hits" % (
-        tag, w, h, nr, best["kernel_ms"], best["primary_ms"], best["shadow_ms"], best["shade_ms"], best["queued_hits"], best["queued_groups"], best["queued_walks"], best["primary_hits"]), flush=True)
+        img, st = sc.render(width=w, height=h, nb_ray=nr)
+        fast = min(fast, st["kernel_ms"])
+    print("%s %dx%d spp%d: overlapped %.2f ms | serial %.2f ms  primary %.2f  shadow %.2f  shade %.2f  queued %d hits -> %d sub-items (%d walks) of %d hits" % (
+        tag, w, h, nr, fast, best["kernel_ms"], best["primary_ms"], best["shadow_ms"], best["shade_ms"], best["queued_hits"], best["queued_groups"], best["queued_walks"], best["primary_hits"]), flush=True)
