@@ -272,7 +272,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,
                     "h2d_bytes_per_step": int(samples.nbytes + 64), "d2h_bytes_per_step": int(rows * WIDTH * 3),
                     "path": "rtb_scene_set_samples + rtb_render with pinned host buffers"},
-            "gpu_launches": args.steps * (7 * world + (1 if world > 1 else 0)),
+            "gpu_launches": args.steps * (s1["launches"] * world + (1 if world > 1 else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
                          "traffic": None, "kernel": "wavefront chain k_primary -> k_shadow_plan -> k_shadow_queue -> k_shade (one launch each per frame)",
                          "kernel_ms": kernel_ms, "per_kernel_ms": per_kernel, "shadow_queue": queue, "algorithmic_flops_per_launch": flops / world,

@@ -10,6 +10,6 @@ python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
 python scripts/profile_frame.py 3840 2160 4 3 > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:k_trace_frame -s 1 -c 1 -f -o gpurun_out/prof_trace \
+ncu --set full --clock-control none --import-source on -k regex:k_shadow_lists -s 2 -c 1 -f -o gpurun_out/prof_trace \
     python scripts/profile_frame.py 3840 2160 4 3 > gpurun_out/ncu_full.log 2>&1
 echo done
