@@ -78,6 +78,9 @@ typedef struct {
     uint32_t queued_hits;            /* hit points whose shadow rays needed the BVH (shadow queue length) */
     uint32_t queued_groups;          /* (hit point, light-sample group) pairs left after the per-group bundle test */
     uint32_t queued_walks;           /* ... of which need a per-ray BVH walk (not just a short candidate list) */
+    uint32_t grid_cells, grid_entries, grid_big;   /* light grids in use for this call (0 = list / walk path): cells, entries,
+                                                      primitives outside the grids */
+    float grid_build_ms;             /* device time of the last grid build (once per sample table, not per frame) */
 } rtb_stats;
 
 typedef struct {

@@ -36,7 +36,8 @@ class Stats(C.Structure):
     _fields_ = [("primary_rays", C.c_uint64), ("primary_hits", C.c_uint64), ("shadow_rays", C.c_uint64),
                 ("shadow_occluded", C.c_uint64), ("box_tests", C.c_uint64), ("tri_tests", C.c_uint64),
                 ("kernel_ms", C.c_float), ("launches", C.c_uint32), ("primary_ms", C.c_float), ("shadow_ms", C.c_float),
-                ("shade_ms", C.c_float), ("queued_hits", C.c_uint32), ("queued_groups", C.c_uint32), ("queued_walks", C.c_uint32)]
+                ("shade_ms", C.c_float), ("queued_hits", C.c_uint32), ("queued_groups", C.c_uint32), ("queued_walks", C.c_uint32),
+                ("grid_cells", C.c_uint32), ("grid_entries", C.c_uint32), ("grid_big", C.c_uint32), ("grid_build_ms", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

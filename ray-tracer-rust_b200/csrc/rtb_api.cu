@@ -16,6 +16,9 @@ struct RtbBuildInfo { uint32_t n_nodes, max_depth, iterations; float sah_cost, b
 cudaError_t rtb_build_scene(const float*, const float*, const int*, uint32_t, float4*, float4*, float4**, int32_t*, RtbBuildInfo*, cudaStream_t);
 cudaError_t rtb_tie_rank_device(const float4* d_tris, uint32_t n, int* d_rank_out, float4* d_colors4, cudaStream_t st);
 cudaError_t rtb_launch_trace(const TraceArgs&, bool, cudaStream_t, cudaEvent_t*);
+cudaError_t rtb_grid_scene_stats(RtbGrid&, const float4*, uint32_t, cudaStream_t);
+cudaError_t rtb_grid_build(RtbGrid&, const float4*, uint32_t, const float4*, uint32_t, float, cudaStream_t);
+void rtb_grid_free(RtbGrid&);
 cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, float*, cudaStream_t);
 cudaError_t rtb_launch_light_groups(const float4*, const float*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint16_t*, float*, cudaStream_t);
 cudaError_t rtb_launch_deinterleave(const uint8_t*, uint64_t, uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, cudaStream_t);
@@ -61,6 +64,10 @@ struct rtb_scene {
     cudaEvent_t evp[4 * 32];                     // per-chunk events around the wavefront kernels (per-kernel times in rtb_stats)
     uint32_t timed_chunks, n_chunks;
     uint64_t chunk_rays;                         // rays per wavefront chunk (RTB200_CHUNK_RAYS, default 16 Mi)
+    RtbGrid grid;                                // light grids (rtb_grid.cu), rebuilt when the sample table or the light-point count changes
+    uint64_t samples_version;
+    int shadow_mode;                             // RTB200_SHADOW: 0 auto (grid when applicable), 1 lists/walk only, 2 grid (same as auto)
+    float grid_cell_factor;                      // RTB200_GRID_CELL: cell size / log-mean primitive extent
 };
 
 // ---- Color::to_rgba threshold table (color.rs:10-33) ---------------------------------------
@@ -131,6 +138,7 @@ void rtb_scene_destroy(rtb_scene* s) {
         if (s->ev_join[k]) cudaEventDestroy(s->ev_join[k]);
     }
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+    rtb_grid_free(s->grid);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -167,6 +175,9 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     for (int k = 0; k < 4 * 32; ++k) TRY_(cudaEventCreate(&s->evp[k]));
     s->chunk_rays = 16ull << 20;
     if (const char* env = getenv("RTB200_CHUNK_RAYS")) { const long long v = atoll(env); if (v > 0) s->chunk_rays = (uint64_t)v; }
+    s->shadow_mode = 0; s->grid_cell_factor = 0.5f;
+    if (const char* env = getenv("RTB200_SHADOW")) s->shadow_mode = !strcmp(env, "lists") ? 1 : (!strcmp(env, "grid") ? 2 : 0);
+    if (const char* env = getenv("RTB200_GRID_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->grid_cell_factor = v; }
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
     for (int k = 0; k < 2; ++k) {
@@ -190,6 +201,7 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
             TRY_(rtb_tie_rank_device(s->d_tris, n, nullptr, s->d_colors4, s->stream));
         }
         TRY_(cudaStreamSynchronize(s->stream));
+        TRY_(rtb_grid_scene_stats(s->grid, s->d_tris, n, s->stream));
         if (s->info.max_depth > RTB_STACK_SIZE - 1) {
             rc = fail(RTB_ERR_LIMIT, "BVH depth %u exceeds traversal stack %d", s->info.max_depth, RTB_STACK_SIZE);
             goto cleanup;
@@ -220,6 +232,7 @@ int rtb_scene_set_samples(rtb_scene* s, const float* samples, uint32_t n_pairs) 
     }
     CUDA_TRY(cudaMemcpyAsync(s->d_samples, samples, (size_t)n_pairs * sizeof(float2), cudaMemcpyHostToDevice, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->samples_version++;
     return RTB_OK;
 }
 
@@ -266,11 +279,21 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     }
     CUDA_TRY(rtb_launch_light_groups(s->d_light_pts, s->d_light_box, p->nb_ray, p->nb_light_sample, s->n_samples, n_groups, group_size,
                                      use_perm ? s->d_light_perm : nullptr, s->d_light_gbox, st));
+    // light grids: one per light point the frame addresses; cached until the table or that count changes
+    if (s->shadow_mode != 1 && p->nb_ray && p->nb_light_sample &&
+        !(s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need)) {
+        CUDA_TRY(rtb_grid_build(s->grid, s->d_tris, s->n_tris, s->d_light_pts, (uint32_t)need, s->grid_cell_factor, st));
+        s->grid.key_set = true; s->grid.key_samples = s->samples_version; s->grid.key_n_lights = (uint32_t)need;
+    }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
     memset(a, 0, sizeof(*a));
     a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_box = s->d_light_box;
     a->light_perm = use_perm ? s->d_light_perm : nullptr;
     a->light_gbox = s->d_light_gbox; a->n_groups = n_groups; a->group_size = group_size;
+    if (s->shadow_mode != 1 && s->grid.valid && s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need) {
+        a->grid_lights = s->grid.d_lights; a->grid_cell_start = s->grid.d_cell_start; a->grid_entries = s->grid.d_entries;
+        a->grid_big = s->grid.d_big; a->grid_n_big = s->grid.n_big;
+    }
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
     a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;
     a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;
@@ -397,7 +420,10 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
         st->shadow_rays = h[RTB_CTR_SHADOW]; st->shadow_occluded = h[RTB_CTR_OCCLUDED];
         st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
         st->kernel_ms = ms;
-        st->launches = 3 + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? 3 : 0));   // light table, bounds, groups + per chunk
+        const bool grid = s->shadow_mode != 1 && s->grid.valid;
+        st->launches = 3 + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? (grid ? 1 : 3) : 0));   // light table, bounds, groups + per chunk
+        st->grid_cells = grid ? s->grid.total_cells : 0; st->grid_entries = grid ? s->grid.total_entries : 0;
+        st->grid_big = grid ? s->grid.n_big : 0; st->grid_build_ms = grid ? s->grid.build_ms : 0.0f;
         st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];
         st->queued_hits = (uint32_t)h[RTB_CTR_QUEUED]; st->queued_groups = (uint32_t)h[RTB_CTR_PAIRS];
         st->queued_walks = (uint32_t)h[RTB_CTR_WALKS];

@@ -9,6 +9,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <float.h>
+#include <string.h>
+#include <math.h>
 
 #define RTB_STACK_SIZE 64          // traversal stack entries (binary BVH depth limit)
 #define RTB_CHILD_NONE 0x7fffffff  // absent child (single-primitive scenes)
@@ -41,6 +43,48 @@ __host__ __device__ __forceinline__ f3 normalize3(f3 a) {
 // unfused f32 arithmetic (host compilers are given -ffp-contract=off).
 struct CameraBasis { f3 u, v, w, eye; float distance; };
 
+// ---- light grids (rtb_grid.cu) --------------------------------------------------------------------------------------
+#define RTB_GRID_MAX_LIGHTS 1024   // light points a frame may use for the grid path (else the list / walk path)
+#define RTB_GRID_MAX_BIG 64        // primitives that cannot be rasterised and are tested by every ray
+
+struct GridLight {                 // one per light point
+    float px, py, pz, H;           // the point, H = py - y_plane
+    float x0, z0, cell, inv_cell;  // grid origin and cell size in plane units
+    int nx, nz;                    // cells
+    uint32_t cell_base, pad;       // first cell of this grid in cell_start
+};
+
+struct GridArgs {                  // build-time arguments
+    const float4* tris; uint32_t n_tris;
+    const float4* light_pts; uint32_t n_lights;
+    float y_plane, cell0;
+    GridLight* lights;
+    unsigned int* lbounds;         // per light: ordered-uint min x, min z, max x, max z of the projections
+    uint32_t* prim_flags;          // per primitive: 1 = "big" (not rasterised, tested by every ray)
+    uint32_t* cell_start;          // total_cells + 1 offsets into entries
+    uint32_t* cell_fill;           // per cell count / cursor
+    int* entries;
+    int* big_list;
+    uint32_t* ctl;                 // [0] total cells [1] big primitives
+    uint32_t cell_cap;
+};
+
+struct RtbGrid {                   // host-side owner of the light grids of one scene (rtb_grid.cu)
+    float y_min, mean_extent; bool stats_ok;
+    GridLight* d_lights; unsigned int* d_lbounds; uint32_t* d_prim_flags; uint32_t* d_cell_start; uint32_t* d_cell_fill;
+    int* d_entries; int* d_big; uint32_t* d_ctl; void* d_cub;
+    size_t lights_cap, lbounds_cap, flags_cap, cell_start_cap, cell_fill_cap, entries_cap, big_cap, ctl_cap, cub_bytes;
+    bool valid; uint32_t n_lights, n_big, total_cells, total_entries; float build_ms;
+    // cache key: the grids depend on the sample table and on how many of its entries the frame addresses
+    uint64_t key_samples; uint32_t key_n_lights; bool key_set;
+};
+
+// hit record / queue item words (rtb_trace.cu)
+#define RTB_REC_MISS 0x7fffffffu     // record word: no hit
+#define RTB_REC_QUEUED 0x80000000u   // record word: low 31 bits = shadow-queue slot
+#define RTB_REC_SELF 0x40000000u     // prim word: the hit primitive's own leaf is reachable (tested per ray in k_shade)
+#define RTB_PRIM_MASK 0x3fffffffu
+
 // Everything a trace kernel needs, passed by value as a kernel parameter.
 struct TraceArgs {
     const float4* __restrict__ tris;     // 3 float4 per primitive: {v0,n.x} {v1,n.y} {v2,n.z}
@@ -65,6 +109,8 @@ struct TraceArgs {
     uint4* sublists;                     // {hit slot, group, pool offset, n} per pair with a complete candidate list
     int* cand_pool;                      // candidate primitives of the list pairs (bump-allocated by k_shadow_plan)
     uint32_t pool_cap;
+    // light grids (rtb_grid.cu); grid_lights == nullptr: list / walk path
+    const GridLight* grid_lights; const uint32_t* grid_cell_start; const int* grid_entries; const int* grid_big; uint32_t grid_n_big;
     uint32_t* masks;                     // mask_words per queued hit point: bit i = light sample i occluded
     uint32_t* queue_ctl;                 // [0] hit points queued by k_primary [1] k_shadow_plan ticket [2,3] k_shadow_queue ticket [4] walk pairs
                                          // [5] of which with an entry node [6] list pairs [7] pool entries used [8,9] k_shadow_lists ticket

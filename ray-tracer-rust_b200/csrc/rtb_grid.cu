@@ -1,0 +1,415 @@
+// rtb_grid.cu -- light grids: a per-light-point lookup structure for shadow rays.
+//
+// Every shadow ray of a frame ends in one of the FEW light sample points the frame uses: the reference indexes them
+// (r * NB_RAY + i) % len (src/main.rs:194), i.e. 100 points at 1 ray/pixel, 340 at 16 -- the same points for every
+// pixel.  For a fixed light point P, "which primitives can the segment o -> P meet" depends only on the direction in
+// which P sees o: it is a shadow-map query.  So, per light point, every primitive is projected from P onto the
+// horizontal plane y = y_plane below the scene and rasterised CONSERVATIVELY into a 2-D grid of cells, each cell
+// holding the list of primitives whose (dilated) projection touches it.  A shadow ray then projects its own origin o
+// from P onto the same plane, reads one cell and runs the exact tests (rtb_device.cuh) on that cell's few primitives:
+// no BVH walk, no stack, a handful of candidates instead of ~20 node visits.
+//
+// Exactness.  The grid only proposes candidates; acceptance is decided by the same exact expressions as everywhere
+// else, and a shadow ray is occluded iff SOME accepted primitive lies within the light distance (any-hit, see
+// rtb_trace.cu).  What must hold is that the cell read by a ray lists every primitive the exact test could accept.
+// The exact test (Moller-Trumbore in float) accepts only rays that pass within a few ulps of the triangle; the ray's
+// float direction deviates from the line o -> P by at most 4u L; projection magnifies by at most 1/RTB_GRID_TAU; the
+// float evaluation of the projection errs by 8u (|q| + |P|).  All of this is far below the dilation `grid_margin`
+// applied when rasterising.  Primitives that cannot be projected for some light point (a vertex not clearly below it)
+// or that would cover too many cells (the ground) are not rasterised at all: they go to a short "big" list that every
+// ray tests.  Rays whose origin is not clearly below their light point walk the BVH instead (lane_anyhit_walk).
+#include "rtb_device.cuh"
+#include <cub/cub.cuh>
+
+#define RTB_GRID_TAU 0.02f            // a point is projectable from P if P.y - y > TAU * (P.y - y_plane): magnification <= 50
+#define RTB_GRID_MAX_CELLS_PER_PRIM 4096
+#define RTB_GRID_MAX_DIM 8192
+
+__device__ __forceinline__ unsigned int g_f2ord(float f) { const unsigned int b = __float_as_uint(f); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
+__device__ __forceinline__ float g_ord2f(unsigned int o) { return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o); }
+
+// Projection from the light point onto y = y_plane: q = P.xz + (v - P).xz * H / (P.y - v.y), H = P.y - y_plane.
+__device__ __forceinline__ bool grid_project(float px, float py, float pz, float H, f3 v, float& qx, float& qz) {
+    const float dy = py - v.y;
+    if (!(dy > RTB_GRID_TAU * H)) return false;                 // also false for NaN
+    const float s = H / dy;
+    qx = fmaf(v.x - px, s, px);
+    qz = fmaf(v.z - pz, s, pz);
+    return true;
+}
+
+// Dilation (plane units) that covers every difference between "the exact test may accept" and "the ideal line o -> P
+// meets the ideal triangle", see the header comment.
+__device__ __forceinline__ float grid_margin(float cell, float qabs, float px, float pz, float H) {
+    return 0.02f * cell + 0.01f + 4e-5f * (qabs + fabsf(px) + fabsf(pz) + H);
+}
+
+// ---- scene statistics (once per scene): lowest vertex and the log-mean of the primitives' largest box extent ----------
+__global__ void k_grid_scene_stats(const float4* __restrict__ tris, uint32_t n, unsigned int* __restrict__ ymin_ord, double* __restrict__ sumlog,
+                                   unsigned int* __restrict__ count) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 q0 = tris[3 * i], q1 = tris[3 * i + 1], q2 = tris[3 * i + 2];
+    const float ymin = fminf(fminf(q0.y, q1.y), q2.y);
+    if (ymin == ymin) atomicMin(ymin_ord, g_f2ord(ymin));
+    const float ex = fmaxf(fmaxf(q0.x, q1.x), q2.x) - fminf(fminf(q0.x, q1.x), q2.x);
+    const float ey = fmaxf(fmaxf(q0.y, q1.y), q2.y) - ymin;
+    const float ez = fmaxf(fmaxf(q0.z, q1.z), q2.z) - fminf(fminf(q0.z, q1.z), q2.z);
+    const float e = fmaxf(fmaxf(ex, ey), ez);
+    if (e > 0.0f && e < 1e30f) { atomicAdd(sumlog, (double)logf(e)); atomicAdd(count, 1u); }
+}
+
+// ---- pass A: which primitives are "big", and the bounds of each light point's projection ---------------------------
+__global__ void k_grid_classify(GridArgs g) {
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (uint64_t)g.n_lights * g.n_tris) return;
+    const uint32_t light = (uint32_t)(t / g.n_tris), prim = (uint32_t)(t - (uint64_t)light * g.n_tris);
+    const float4 P = g.light_pts[light];
+    const float H = P.y - g.y_plane;
+    const float4 q0 = g.tris[3 * prim], q1 = g.tris[3 * prim + 1], q2 = g.tris[3 * prim + 2];
+    float x[3], z[3];
+    const bool ok = H > 0.0f && grid_project(P.x, P.y, P.z, H, mk3(q0.x, q0.y, q0.z), x[0], z[0]) &&
+                    grid_project(P.x, P.y, P.z, H, mk3(q1.x, q1.y, q1.z), x[1], z[1]) &&
+                    grid_project(P.x, P.y, P.z, H, mk3(q2.x, q2.y, q2.z), x[2], z[2]);
+    if (!ok) { atomicOr(g.prim_flags + prim, 1u); return; }
+    const float x0 = fminf(fminf(x[0], x[1]), x[2]), x1 = fmaxf(fmaxf(x[0], x[1]), x[2]);
+    const float z0 = fminf(fminf(z[0], z[1]), z[2]), z1 = fmaxf(fmaxf(z[0], z[1]), z[2]);
+    const float cells = ((x1 - x0) / g.cell0 + 2.0f) * ((z1 - z0) / g.cell0 + 2.0f);
+    if (!(cells <= (float)RTB_GRID_MAX_CELLS_PER_PRIM)) { atomicOr(g.prim_flags + prim, 1u); return; }
+    unsigned int* b = g.lbounds + 4 * light;
+    atomicMin(b + 0, g_f2ord(x0)); atomicMin(b + 1, g_f2ord(z0)); atomicMax(b + 2, g_f2ord(x1)); atomicMax(b + 3, g_f2ord(z1));
+}
+
+__global__ void k_grid_biglist(GridArgs g) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n_tris || !g.prim_flags[i]) return;
+    const uint32_t k = atomicAdd(g.ctl + 1, 1u);
+    if (k < RTB_GRID_MAX_BIG) g.big_list[k] = (int)i;
+}
+
+// ---- pass B: grid geometry per light point (one block; n_lights <= RTB_GRID_MAX_LIGHTS) ---------------------------------
+__global__ void __launch_bounds__(1024) k_grid_layout(GridArgs g) {
+    __shared__ float s_scale;
+    __shared__ unsigned long long s_total;
+    if (threadIdx.x == 0) { s_scale = 1.0f; s_total = 0ull; }
+    __syncthreads();
+    for (int pass = 0; pass < 2; ++pass) {
+        const float cell = g.cell0 * s_scale;
+        unsigned long long mine = 0;
+        for (uint32_t l = threadIdx.x; l < g.n_lights; l += blockDim.x) {
+            const float4 P = g.light_pts[l];
+            const unsigned int* b = g.lbounds + 4 * l;
+            GridLight G;
+            G.px = P.x; G.py = P.y; G.pz = P.z; G.H = P.y - g.y_plane; G.cell_base = 0; G.nx = 0; G.nz = 0;
+            G.x0 = 0.0f; G.z0 = 0.0f; G.inv_cell = 0.0f; G.cell = cell; G.pad = 0;
+            if (b[0] <= b[2] && b[1] <= b[3] && G.H > 0.0f) {                    // at least one primitive projected
+                const float x0 = g_ord2f(b[0]), z0 = g_ord2f(b[1]), x1 = g_ord2f(b[2]), z1 = g_ord2f(b[3]);
+                const float m = grid_margin(cell, fmaxf(fmaxf(fabsf(x0), fabsf(x1)), fmaxf(fabsf(z0), fabsf(z1))), P.x, P.z, G.H);
+                float c = cell;
+                float nx = ceilf((x1 - x0 + 2.0f * m) / c) + 1.0f, nz = ceilf((z1 - z0 + 2.0f * m) / c) + 1.0f;
+                if (nx > (float)RTB_GRID_MAX_DIM || nz > (float)RTB_GRID_MAX_DIM) {  // huge footprint: coarser cells for this light
+                    c = fmaxf((x1 - x0 + 2.0f * m), (z1 - z0 + 2.0f * m)) / (float)(RTB_GRID_MAX_DIM - 2);
+                    nx = ceilf((x1 - x0 + 2.0f * m) / c) + 1.0f; nz = ceilf((z1 - z0 + 2.0f * m) / c) + 1.0f;
+                }
+                G.x0 = x0 - m; G.z0 = z0 - m; G.cell = c; G.inv_cell = 1.0f / c; G.nx = (int)nx; G.nz = (int)nz;
+                mine += (unsigned long long)G.nx * (unsigned long long)G.nz;
+            }
+            g.lights[l] = G;
+        }
+        atomicAdd(&s_total, mine);
+        __syncthreads();
+        if (pass == 0) {
+            const bool too_many = s_total > (unsigned long long)g.cell_cap;
+            __syncthreads();
+            if (!too_many) break;
+            if (threadIdx.x == 0) { s_scale = sqrtf((float)((double)s_total / (double)g.cell_cap)) * 1.05f; s_total = 0ull; }
+            __syncthreads();
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {                                                       // exclusive scan of the cell counts
+        unsigned long long base = 0;
+        for (uint32_t l = 0; l < g.n_lights; ++l) {
+            g.lights[l].cell_base = (uint32_t)base;
+            base += (unsigned long long)g.lights[l].nx * (unsigned long long)g.lights[l].nz;
+        }
+        g.ctl[0] = base > 0xffffffffull ? 0xffffffffu : (uint32_t)base;           // total cells (the host checks it against cell_cap)
+    }
+}
+
+// ---- passes C / D: conservative rasterisation of every projected primitive into its light point's grid -----------------
+// FILL = false: count per cell (cell_fill);  FILL = true: write the primitive at cell_start[cell] + cursor.
+template <bool FILL>
+__global__ void k_grid_raster(GridArgs g) {
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (uint64_t)g.n_lights * g.n_tris) return;
+    const uint32_t light = (uint32_t)(t / g.n_tris), prim = (uint32_t)(t - (uint64_t)light * g.n_tris);
+    if (g.prim_flags[prim]) return;
+    const GridLight G = g.lights[light];
+    if (G.nx <= 0 || G.nz <= 0) return;
+    const float4 q0 = g.tris[3 * prim], q1 = g.tris[3 * prim + 1], q2 = g.tris[3 * prim + 2];
+    float x[3], z[3];
+    if (!(grid_project(G.px, G.py, G.pz, G.H, mk3(q0.x, q0.y, q0.z), x[0], z[0]) &&
+          grid_project(G.px, G.py, G.pz, G.H, mk3(q1.x, q1.y, q1.z), x[1], z[1]) &&
+          grid_project(G.px, G.py, G.pz, G.H, mk3(q2.x, q2.y, q2.z), x[2], z[2]))) return;   // cannot happen: such a primitive is flagged
+    const float bx0 = fminf(fminf(x[0], x[1]), x[2]), bx1 = fmaxf(fmaxf(x[0], x[1]), x[2]);
+    const float bz0 = fminf(fminf(z[0], z[1]), z[2]), bz1 = fmaxf(fmaxf(z[0], z[1]), z[2]);
+    const float m = grid_margin(G.cell, fmaxf(fmaxf(fabsf(bx0), fabsf(bx1)), fmaxf(fabsf(bz0), fabsf(bz1))), G.px, G.pz, G.H);
+    int cx0 = (int)floorf((bx0 - m - G.x0) * G.inv_cell), cx1 = (int)floorf((bx1 + m - G.x0) * G.inv_cell);
+    int cz0 = (int)floorf((bz0 - m - G.z0) * G.inv_cell), cz1 = (int)floorf((bz1 + m - G.z0) * G.inv_cell);
+    cx0 = max(cx0, 0); cz0 = max(cz0, 0); cx1 = min(cx1, G.nx - 1); cz1 = min(cz1, G.nz - 1);
+    // edge functions of the projected triangle, oriented so that the inside is positive; a cell is skipped when its
+    // m-dilated rectangle lies entirely outside one edge.  Slivers (|area| tiny) use the bounding box alone.
+    float ex[3], ez[3], ec[3];
+    const float area = (x[1] - x[0]) * (z[2] - z[0]) - (x[2] - x[0]) * (z[1] - z[0]);
+    const float sgn = area >= 0.0f ? 1.0f : -1.0f;
+    const bool use_edges = fabsf(area) > 1e-6f * (bx1 - bx0 + bz1 - bz0 + 1e-20f) * (bx1 - bx0 + bz1 - bz0 + 1e-20f);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const int k1 = (k + 1) % 3;
+        ex[k] = -(z[k1] - z[k]) * sgn; ez[k] = (x[k1] - x[k]) * sgn;      // inward normal
+        ec[k] = -(ex[k] * x[k] + ez[k] * z[k]);
+    }
+    for (int cz = cz0; cz <= cz1; ++cz) {
+        const float rz0 = G.z0 + cz * G.cell - m, rz1 = G.z0 + (cz + 1) * G.cell + m;
+        for (int cx = cx0; cx <= cx1; ++cx) {
+            if (use_edges) {
+                const float rx0 = G.x0 + cx * G.cell - m, rx1 = G.x0 + (cx + 1) * G.cell + m;
+                bool out = false;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    // the rectangle corner furthest along the inward normal
+                    const float fx = ex[k] >= 0.0f ? rx1 : rx0, fz = ez[k] >= 0.0f ? rz1 : rz0;
+                    const float e = ex[k] * fx + ez[k] * fz + ec[k];
+                    // rounding of e: a few ulps of the terms; keep the cell unless it is outside by more than that
+                    const float tol = 4e-6f * (fabsf(ex[k] * fx) + fabsf(ez[k] * fz) + fabsf(ec[k]));
+                    out = out || (e < -tol);
+                }
+                if (out) continue;
+            }
+            const uint32_t cell = G.cell_base + (uint32_t)cz * (uint32_t)G.nx + (uint32_t)cx;
+            if (FILL) g.entries[g.cell_start[cell] + atomicAdd(g.cell_fill + cell, 1u)] = (int)prim;
+            else atomicAdd(g.cell_fill + cell, 1u);
+        }
+    }
+}
+
+// ---- the shadow kernel of the grid path -------------------------------------------------------------------------------
+// Any-hit BVH walk of one ray (per-lane stack): the fallback for a ray whose origin is not clearly below its light point.
+template <bool COUNT>
+__device__ __noinline__ bool lane_anyhit_walk(const TraceArgs& a, f3 o, f3 d, float L, int self_prim, const RayCull& c,
+                                              uint32_t& n_box, uint32_t& n_tri, uint32_t& overflow) {
+    if (a.root == RTB_CHILD_NONE) return false;
+    int stack[RTB_STACK_SIZE];
+    int sp = 0, cur = a.root;
+    for (;;) {
+        if (cur >= 0) {
+            const float4* np = a.nodes + 4 * (size_t)cur;
+            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3);
+            const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+            float t0, t1;
+            const bool h0 = node_test(c, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, t0);
+            const bool h1 = node_test(c, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, t1) && (c1 != RTB_CHILD_NONE);
+            if (COUNT) n_box += 2;
+            if (h0 && h1) {
+                const bool swap = t1 < t0;
+                if (sp < RTB_STACK_SIZE) stack[sp++] = swap ? c0 : c1; else overflow = 1;
+                cur = swap ? c1 : c0;
+                continue;
+            }
+            if (h0) { cur = c0; continue; }
+            if (h1) { cur = c1; continue; }
+        } else {
+            if (COUNT) n_tri += 1;
+            if (prim_occludes(a.tris, ~cur, ~cur == self_prim, o, d, L, c)) return true;
+        }
+        if (sp == 0) return false;
+        cur = stack[--sp];
+    }
+}
+
+// One lane per ray (queued hit point, light sample i).  32 consecutive rays = 32 consecutive queue slots (a pixel tile
+// of k_primary) with the SAME sample, hence normally the same light point: the lanes read neighbouring cells of one grid.
+// Result: bit i of the hit point's mask (zeroed by k_primary) = sample i occluded.
+template <bool COUNT>
+__global__ void __launch_bounds__(256) k_shadow_grid(const TraceArgs a) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t n_items = a.queue_ctl[0];
+    const uint64_t total = (uint64_t)((n_items + 31) / 32) * 32 * a.nb_light_sample;
+    unsigned long long* ticket = reinterpret_cast<unsigned long long*>(a.queue_ctl + 8);
+    uint32_t n_box = 0, n_tri = 0, overflow = 0;
+    for (;;) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(ticket, 32ull);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= total) break;
+        const uint64_t chunk = base >> 5;
+        const uint32_t it = (uint32_t)(chunk / a.nb_light_sample) * 32 + lane;
+        const uint32_t i = (uint32_t)(chunk % a.nb_light_sample);
+        if (it >= n_items) continue;
+        const float4* ip = a.items + RTB_ITEM_F4 * (size_t)it;
+        const float4 i0 = __ldg(ip), i1 = __ldg(ip + 1);
+        const uint32_t r = __float_as_uint(i0.x) / a.n_pix_padded;
+        const int self_prim = (int)(__float_as_uint(i0.y) & RTB_PRIM_MASK);
+        const f3 o = mk3(i1.x, i1.y, i1.z);
+        const uint32_t idx = (uint32_t)(((uint64_t)r * a.nb_ray + i) % a.n_samples);            // (r*NB_RAY + i) % len, src/main.rs:194
+        const float4 lp = __ldg(a.light_pts + idx);
+        float L; f3 d;
+        normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);               // Ray::new + distance (src/main.rs:201-202)
+        const RayCull c = make_cull(o, d);
+        const float4* gp = reinterpret_cast<const float4*>(a.grid_lights + idx);
+        const float4 g0 = __ldg(gp), g1 = __ldg(gp + 1), g2 = __ldg(gp + 2);      // {px,py,pz,H} {x0,z0,cell,inv_cell} {nx,nz,cell_base,-}
+        bool occluded = false;
+        const float dy = g0.y - o.y;
+        if (dy > RTB_GRID_TAU * g0.w) {
+            const float s = g0.w / dy;
+            const float fx = (fmaf(o.x - g0.x, s, g0.x) - g1.x) * g1.w, fz = (fmaf(o.z - g0.z, s, g0.z) - g1.y) * g1.w;
+            const int nx = __float_as_int(g2.x), nz = __float_as_int(g2.y);
+            if (fx >= 0.0f && fz >= 0.0f && fx < (float)nx && fz < (float)nz) {       // false for NaN
+                const uint32_t cell = __float_as_uint(g2.z) + (uint32_t)fz * (uint32_t)nx + (uint32_t)fx;
+                const uint32_t beg = __ldg(a.grid_cell_start + cell), end = __ldg(a.grid_cell_start + cell + 1);
+                for (uint32_t k = beg; k < end && !occluded; ++k) {
+                    const int prim = __ldg(a.grid_entries + k);
+                    if (COUNT) n_tri += 1;
+                    occluded = prim_occludes(a.tris, prim, prim == self_prim, o, d, L, c);
+                }
+            }
+            for (uint32_t k = 0; k < a.grid_n_big && !occluded; ++k) {              // primitives outside the grids (the ground)
+                const int prim = __ldg(a.grid_big + k);
+                if (COUNT) n_tri += 1;
+                occluded = prim_occludes(a.tris, prim, prim == self_prim, o, d, L, c);
+            }
+        } else {
+            occluded = lane_anyhit_walk<COUNT>(a, o, d, L, self_prim, c, n_box, n_tri, overflow);
+        }
+        if (occluded) atomicOr(a.masks + (size_t)it * a.mask_words + (i >> 5), 1u << (i & 31));
+    }
+    if (__any_sync(0xffffffffu, overflow != 0) && lane == 0) atomicAdd(a.counters + RTB_CTR_OVERFLOW, 1ull);
+    if (COUNT) {
+        unsigned long long nb = n_box, nt = n_tri;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) { nb += __shfl_down_sync(0xffffffffu, nb, off); nt += __shfl_down_sync(0xffffffffu, nt, off); }
+        if (lane == 0) { atomicAdd(a.counters + RTB_CTR_BOX, nb); atomicAdd(a.counters + RTB_CTR_TRI, nt); }
+    }
+}
+
+cudaError_t rtb_launch_shadow_grid(const TraceArgs& a, bool count, unsigned blocks, cudaStream_t st) {
+    if (count) k_shadow_grid<true><<<blocks, 256, 0, st>>>(a);
+    else k_shadow_grid<false><<<blocks, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+// ---- host side: scene statistics and the per-light-table build ---------------------------------------------------------
+__global__ void k_grid_init(unsigned int* __restrict__ lbounds, uint32_t n_lights, uint32_t* __restrict__ prim_flags, uint32_t n_tris, uint32_t* __restrict__ ctl) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_lights) { lbounds[4 * i] = 0xffffffffu; lbounds[4 * i + 1] = 0xffffffffu; lbounds[4 * i + 2] = 0u; lbounds[4 * i + 3] = 0u; }
+    if (i < n_tris) prim_flags[i] = 0u;
+    if (i < 4) ctl[i] = 0u;
+}
+
+#define GRID_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
+
+template <typename T>
+static cudaError_t grid_reserve(T** p, size_t* cap, size_t need) {
+    if (need <= *cap) return cudaSuccess;
+    cudaFree(*p); *p = nullptr; *cap = 0;
+    GRID_CK(cudaMalloc(p, need * sizeof(T)));
+    *cap = need;
+    return cudaSuccess;
+}
+
+cudaError_t rtb_grid_scene_stats(RtbGrid& G, const float4* d_tris, uint32_t n, cudaStream_t st) {
+    G.stats_ok = false;
+    if (n == 0) return cudaSuccess;
+    unsigned int* d_u = nullptr; double* d_d = nullptr;
+    GRID_CK(cudaMalloc(&d_u, 2 * sizeof(unsigned int)));
+    cudaError_t e = cudaMalloc(&d_d, sizeof(double));
+    unsigned int h_u[2] = {0xffffffffu, 0u}; double h_d = 0.0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_u, h_u, sizeof(h_u), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_d, &h_d, sizeof(h_d), cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess) { k_grid_scene_stats<<<(n + 255) / 256, 256, 0, st>>>(d_tris, n, d_u, d_d, d_u + 1); e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_u, d_u, sizeof(h_u), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h_d, d_d, sizeof(h_d), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d_u); cudaFree(d_d);
+    if (e != cudaSuccess) return e;
+    if (h_u[0] != 0xffffffffu && h_u[1] > 0) {
+        const unsigned int o = h_u[0];
+        unsigned int bits = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+        float ymin; memcpy(&ymin, &bits, 4);
+        G.y_min = ymin;
+        G.mean_extent = (float)exp(h_d / (double)h_u[1]);
+        G.stats_ok = ymin == ymin && G.mean_extent > 0.0f;
+    }
+    return cudaSuccess;
+}
+
+void rtb_grid_free(RtbGrid& G) {
+    cudaFree(G.d_lights); cudaFree(G.d_lbounds); cudaFree(G.d_prim_flags); cudaFree(G.d_cell_start); cudaFree(G.d_cell_fill);
+    cudaFree(G.d_entries); cudaFree(G.d_big); cudaFree(G.d_ctl); cudaFree(G.d_cub);
+    memset(&G, 0, sizeof(G));
+}
+
+// Builds the grids for the light points d_light_pts[0..n_lights).  On success G.valid says whether the grid path applies
+// (false: too many light points / primitives, too many un-rasterisable primitives, or the table would be too large).
+cudaError_t rtb_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, const float4* d_light_pts, uint32_t n_lights, float cell_factor,
+                           cudaStream_t st) {
+    G.valid = false; G.n_lights = n_lights; G.n_big = 0; G.total_cells = 0; G.total_entries = 0; G.build_ms = 0.0f;
+    const uint64_t work = (uint64_t)n_lights * n_tris;
+    if (!G.stats_ok || n_lights == 0 || n_lights > RTB_GRID_MAX_LIGHTS || n_tris == 0 || work > (256ull << 20)) return cudaSuccess;
+    const size_t CELL_CAP = 64u << 20, ENTRY_CAP = 512u << 20;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    GRID_CK(cudaEventCreate(&ev0)); GRID_CK(cudaEventCreate(&ev1));
+    GRID_CK(cudaEventRecord(ev0, st));
+    GRID_CK(grid_reserve(&G.d_lights, &G.lights_cap, (size_t)n_lights));
+    GRID_CK(grid_reserve(&G.d_lbounds, &G.lbounds_cap, (size_t)n_lights * 4));
+    GRID_CK(grid_reserve(&G.d_prim_flags, &G.flags_cap, (size_t)n_tris));
+    GRID_CK(grid_reserve(&G.d_big, &G.big_cap, (size_t)RTB_GRID_MAX_BIG));
+    GRID_CK(grid_reserve(&G.d_ctl, &G.ctl_cap, (size_t)4));
+    GridArgs g; memset(&g, 0, sizeof(g));
+    g.tris = d_tris; g.n_tris = n_tris; g.light_pts = d_light_pts; g.n_lights = n_lights;
+    // the plane sits a little below the lowest vertex so that ground-level origins project with a finite scale
+    g.y_plane = G.y_min - 1.0f - 1e-3f * fabsf(G.y_min);
+    g.cell0 = G.mean_extent * cell_factor;
+    g.lights = G.d_lights; g.lbounds = G.d_lbounds; g.prim_flags = G.d_prim_flags; g.big_list = G.d_big; g.ctl = G.d_ctl;
+    g.cell_cap = (uint32_t)CELL_CAP;
+    const unsigned nmax = n_lights > n_tris ? n_lights : n_tris;
+    k_grid_init<<<(nmax + 255) / 256, 256, 0, st>>>(G.d_lbounds, n_lights, G.d_prim_flags, n_tris, G.d_ctl);
+    const unsigned gw = (unsigned)((work + 255) / 256);
+    k_grid_classify<<<gw, 256, 0, st>>>(g);
+    k_grid_biglist<<<(n_tris + 255) / 256, 256, 0, st>>>(g);
+    k_grid_layout<<<1, 1024, 0, st>>>(g);
+    GRID_CK(cudaGetLastError());
+    uint32_t h_ctl[4] = {0, 0, 0, 0};
+    GRID_CK(cudaMemcpyAsync(h_ctl, G.d_ctl, sizeof(h_ctl), cudaMemcpyDeviceToHost, st));
+    GRID_CK(cudaStreamSynchronize(st));
+    G.total_cells = h_ctl[0]; G.n_big = h_ctl[1];
+    if (G.n_big > RTB_GRID_MAX_BIG || G.total_cells > CELL_CAP) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return cudaSuccess; }
+    const size_t nc = (size_t)G.total_cells + 1;
+    GRID_CK(grid_reserve(&G.d_cell_start, &G.cell_start_cap, nc));
+    GRID_CK(grid_reserve(&G.d_cell_fill, &G.cell_fill_cap, nc));
+    g.cell_start = G.d_cell_start; g.cell_fill = G.d_cell_fill;
+    GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
+    k_grid_raster<false><<<gw, 256, 0, st>>>(g);
+    GRID_CK(cudaGetLastError());
+    size_t need = 0;
+    GRID_CK(cub::DeviceScan::ExclusiveSum(nullptr, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
+    if (need > G.cub_bytes) { cudaFree(G.d_cub); G.d_cub = nullptr; G.cub_bytes = 0; GRID_CK(cudaMalloc(&G.d_cub, need)); G.cub_bytes = need; }
+    GRID_CK(cub::DeviceScan::ExclusiveSum(G.d_cub, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
+    uint32_t h_total = 0;
+    GRID_CK(cudaMemcpyAsync(&h_total, G.d_cell_start + G.total_cells, sizeof(h_total), cudaMemcpyDeviceToHost, st));
+    GRID_CK(cudaStreamSynchronize(st));
+    G.total_entries = h_total;
+    if ((size_t)h_total > ENTRY_CAP) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return cudaSuccess; }
+    GRID_CK(grid_reserve(&G.d_entries, &G.entries_cap, (size_t)h_total + 1));
+    g.entries = G.d_entries;
+    GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
+    k_grid_raster<true><<<gw, 256, 0, st>>>(g);
+    GRID_CK(cudaGetLastError());
+    GRID_CK(cudaEventRecord(ev1, st));
+    GRID_CK(cudaEventSynchronize(ev1));
+    GRID_CK(cudaEventElapsedTime(&G.build_ms, ev0, ev1));
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    G.valid = true;
+    return cudaSuccess;
+}

@@ -35,6 +35,7 @@ pub struct RtbStats {
     pub box_tests: u64, pub tri_tests: u64, pub kernel_ms: f32, pub launches: u32,
     pub primary_ms: f32, pub shadow_ms: f32, pub shade_ms: f32, pub queued_hits: u32,
     pub queued_groups: u32, pub queued_walks: u32,
+    pub grid_cells: u32, pub grid_entries: u32, pub grid_big: u32, pub grid_build_ms: f32,
 }
 
 #[repr(C)]

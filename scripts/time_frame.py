@@ -25,5 +25,6 @@ for (w, h, nr) in ((1920, 1080, 1), (3840, 2160, 16)):
         if best is None or st["kernel_ms"] < best["kernel_ms"]: best = st
         img, st = sc.render(width=w, height=h, nb_ray=nr)
         fast = min(fast, st["kernel_ms"])
+    print("   grid: cells %d entries %d big %d build %.2f ms" % (best["grid_cells"], best["grid_entries"], best["grid_big"], best["grid_build_ms"]))
     print("%s %dx%d spp%d: overlapped %.2f ms | serial %.2f ms  primary %.2f  shadow %.2f  shade %.2f  queued %d hits -> %d sub-items (%d walks) of %d hits" % (
         tag, w, h, nr, fast, best["kernel_ms"], best["primary_ms"], best["shadow_ms"], best["shade_ms"], best["queued_hits"], best["queued_groups"], best["queued_walks"], best["primary_hits"]), flush=True)

@@ -270,14 +270,14 @@ def test_chunked_wavefront_equals_single_pass(rtb, big_bunny_inputs, monkeypatch
     ref, st_ref = ref_sc.render(profile=True, **kw)
     pix = S.stratified_pixels(640, 360, 7, seed=2)
     ref_list = ref_sc.render_pixels(pix, **kw)
-    assert st_ref["launches"] == 3 + 5
+    assert st_ref["launches"] in (3 + 5, 3 + 3)            # list / walk path or light-grid path
     monkeypatch.setenv("RTB200_CHUNK_RAYS", "30000")
     sc = rtb.Scene(v, c); sc.set_samples(smp)
     got, st = sc.render(**kw)                      # chunks overlapped on two worker streams
     assert (got == ref).all()
     got2, st2 = sc.render(profile=True, **kw)      # chunks in sequence on one stream, per-kernel times
     assert (got2 == ref).all() and st2["shade_ms"] > 0 and st2["launches"] == st["launches"]
-    assert st["launches"] > 3 + 5 * 10
+    assert st["launches"] > 3 + 3 * 10
     for k in ("primary_hits", "shadow_rays", "shadow_occluded", "queued_hits", "queued_groups"):
         assert st[k] == st_ref[k], k
     got_list = sc.render_pixels(pix, **kw)

@@ -32,7 +32,7 @@ def test_library_exports_every_declared_symbol(rtb):
 def test_struct_layouts_match_header(rtb):
     import ctypes as C
     assert C.sizeof(rtb.binding.RenderParams) == 4 * 4 + 10 * 4 + 4 * 4
-    assert C.sizeof(rtb.binding.Stats) == 6 * 8 + 8 + 16 + 8
+    assert C.sizeof(rtb.binding.Stats) == 6 * 8 + 8 + 16 + 8 + 16
     assert C.sizeof(rtb.binding.SceneDesc) == 8 + 3 * 8 + 9 * 4 + 4
     assert C.sizeof(rtb.binding.SceneInfo) == 24
 
