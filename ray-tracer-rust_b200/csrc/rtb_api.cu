@@ -175,7 +175,7 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     for (int k = 0; k < 4 * 32; ++k) TRY_(cudaEventCreate(&s->evp[k]));
     s->chunk_rays = 16ull << 20;
     if (const char* env = getenv("RTB200_CHUNK_RAYS")) { const long long v = atoll(env); if (v > 0) s->chunk_rays = (uint64_t)v; }
-    s->shadow_mode = 0; s->grid_cell_factor = 0.5f;
+    s->shadow_mode = 0; s->grid_cell_factor = 0.25f;
     if (const char* env = getenv("RTB200_SHADOW")) s->shadow_mode = !strcmp(env, "lists") ? 1 : (!strcmp(env, "grid") ? 2 : 0);
     if (const char* env = getenv("RTB200_GRID_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->grid_cell_factor = v; }
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
@@ -308,14 +308,14 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
 
 // Grows (never shrinks) the wavefront buffers of the scene to hold one chunk of `rays` rays: worst case every ray hits,
 // is queued and keeps all its light-sample groups.
-static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_groups, uint32_t mask_words) {
+static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_groups, uint32_t mask_words, bool lists) {
     if (rays > b.rays_cap) {
         cudaFree(b.d_records); cudaFree(b.d_items); b.d_records = nullptr; b.d_items = nullptr; b.rays_cap = 0;
         CUDA_TRY(cudaMalloc(&b.d_records, rays * sizeof(uint2)));
         CUDA_TRY(cudaMalloc(&b.d_items, rays * RTB_ITEM_F4 * sizeof(float4)));
         b.rays_cap = rays;
     }
-    const uint64_t sub_need = rays * n_groups;
+    const uint64_t sub_need = lists ? rays * n_groups : 0;     // pair queues and candidate pool: list / walk path only
     if (sub_need > b.sub_cap) {
         cudaFree(b.d_subitems); cudaFree(b.d_sublists); b.d_subitems = nullptr; b.d_sublists = nullptr; b.sub_cap = 0;
         CUDA_TRY(cudaMalloc(&b.d_subitems, (sub_need ? sub_need : 1) * sizeof(uint4)));
@@ -324,7 +324,7 @@ static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_g
     }
     // candidate pool: 16 entries per ray on average is far above anything measured (big_bunny: 2.4); a full pool is not
     // an error, the remaining pairs walk the BVH instead
-    uint64_t pool_need = rays * 16;
+    uint64_t pool_need = lists ? rays * 16 : 0;
     if (pool_need > 0xfffffff0ull) pool_need = 0xfffffff0ull;
     if (pool_need > b.pool_cap) {
         cudaFree(b.d_cand_pool); b.d_cand_pool = nullptr; b.pool_cap = 0;
@@ -367,7 +367,7 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
     // runs on worker stream c & 1 with buffer set c & 1; the workers start after the caller's stream and it waits for them.
     const bool overlap = !timed && n_chunks > 1;
     for (int k = 0; k < (overlap ? 2 : 1); ++k) {
-        const int rc = reserve_wavefront(s->wb[k], npp_max * per_pixel, a.n_groups, a.mask_words);
+        const int rc = reserve_wavefront(s->wb[k], npp_max * per_pixel, a.n_groups, a.mask_words, a.grid_lights == nullptr);
         if (rc != RTB_OK) return rc;
     }
     if (overlap) {

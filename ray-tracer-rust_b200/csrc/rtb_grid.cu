@@ -230,59 +230,61 @@ __device__ __noinline__ bool lane_anyhit_walk(const TraceArgs& a, f3 o, f3 d, fl
 
 // One lane per ray (queued hit point, light sample i).  32 consecutive rays = 32 consecutive queue slots (a pixel tile
 // of k_primary) with the SAME sample, hence normally the same light point: the lanes read neighbouring cells of one grid.
-// Result: bit i of the hit point's mask (zeroed by k_primary) = sample i occluded.
+// Result: the transposed occlusion masks described at the end of the loop.
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_shadow_grid(const TraceArgs a) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t n_items = a.queue_ctl[0];
-    const uint64_t total = (uint64_t)((n_items + 31) / 32) * 32 * a.nb_light_sample;
-    unsigned long long* ticket = reinterpret_cast<unsigned long long*>(a.queue_ctl + 8);
+    const uint32_t total = ((n_items + 31) / 32) * a.nb_light_sample;          // tickets: (block of 32 hit points, sample i)
     uint32_t n_box = 0, n_tri = 0, overflow = 0;
     for (;;) {
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(ticket, 32ull);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= total) break;
-        const uint64_t chunk = base >> 5;
-        const uint32_t it = (uint32_t)(chunk / a.nb_light_sample) * 32 + lane;
-        const uint32_t i = (uint32_t)(chunk % a.nb_light_sample);
-        if (it >= n_items) continue;
-        const float4* ip = a.items + RTB_ITEM_F4 * (size_t)it;
-        const float4 i0 = __ldg(ip), i1 = __ldg(ip + 1);
-        const uint32_t r = __float_as_uint(i0.x) / a.n_pix_padded;
-        const int self_prim = (int)(__float_as_uint(i0.y) & RTB_PRIM_MASK);
-        const f3 o = mk3(i1.x, i1.y, i1.z);
-        const uint32_t idx = (uint32_t)(((uint64_t)r * a.nb_ray + i) % a.n_samples);            // (r*NB_RAY + i) % len, src/main.rs:194
-        const float4 lp = __ldg(a.light_pts + idx);
-        float L; f3 d;
-        normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);               // Ray::new + distance (src/main.rs:201-202)
-        const RayCull c = make_cull(o, d);
-        const float4* gp = reinterpret_cast<const float4*>(a.grid_lights + idx);
-        const float4 g0 = __ldg(gp), g1 = __ldg(gp + 1), g2 = __ldg(gp + 2);      // {px,py,pz,H} {x0,z0,cell,inv_cell} {nx,nz,cell_base,-}
+        uint32_t tk = 0;
+        if (lane == 0) tk = atomicAdd(a.queue_ctl + 8, 1u);
+        tk = __shfl_sync(0xffffffffu, tk, 0);
+        if (tk >= total) break;
+        const uint32_t blk = tk / a.nb_light_sample, i = tk - blk * a.nb_light_sample;
+        const uint32_t it = blk * 32 + lane;
         bool occluded = false;
-        const float dy = g0.y - o.y;
-        if (dy > RTB_GRID_TAU * g0.w) {
-            const float s = g0.w / dy;
-            const float fx = (fmaf(o.x - g0.x, s, g0.x) - g1.x) * g1.w, fz = (fmaf(o.z - g0.z, s, g0.z) - g1.y) * g1.w;
-            const int nx = __float_as_int(g2.x), nz = __float_as_int(g2.y);
-            if (fx >= 0.0f && fz >= 0.0f && fx < (float)nx && fz < (float)nz) {       // false for NaN
-                const uint32_t cell = __float_as_uint(g2.z) + (uint32_t)fz * (uint32_t)nx + (uint32_t)fx;
-                const uint32_t beg = __ldg(a.grid_cell_start + cell), end = __ldg(a.grid_cell_start + cell + 1);
-                for (uint32_t k = beg; k < end && !occluded; ++k) {
-                    const int prim = __ldg(a.grid_entries + k);
+        if (it < n_items) {
+            const float4* ip = a.items + RTB_ITEM_F4 * (size_t)it;
+            const float4 i0 = __ldg(ip), i1 = __ldg(ip + 1);
+            const int self_prim = (int)(__float_as_uint(i0.y) & RTB_PRIM_MASK);
+            const f3 o = mk3(i1.x, i1.y, i1.z);
+            uint32_t idx = __float_as_uint(i0.w) + i;                            // (r*NB_RAY + i) % len, src/main.rs:194
+            if (idx >= a.n_samples) idx %= a.n_samples;
+            const float4 lp = __ldg(a.light_pts + idx);
+            float L; f3 d;
+            normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);           // Ray::new + distance (src/main.rs:201-202)
+            const RayCull c = make_cull(o, d);
+            const float4* gp = reinterpret_cast<const float4*>(a.grid_lights + idx);
+            const float4 g0 = __ldg(gp), g1 = __ldg(gp + 1), g2 = __ldg(gp + 2);  // {px,py,pz,H} {x0,z0,cell,inv_cell} {nx,nz,cell_base,-}
+            const float dy = g0.y - o.y;
+            if (dy > RTB_GRID_TAU * g0.w) {
+                const float s = g0.w / dy;
+                const float fx = (fmaf(o.x - g0.x, s, g0.x) - g1.x) * g1.w, fz = (fmaf(o.z - g0.z, s, g0.z) - g1.y) * g1.w;
+                const int nx = __float_as_int(g2.x), nz = __float_as_int(g2.y);
+                if (fx >= 0.0f && fz >= 0.0f && fx < (float)nx && fz < (float)nz) {   // false for NaN
+                    const uint32_t cell = __float_as_uint(g2.z) + (uint32_t)fz * (uint32_t)nx + (uint32_t)fx;
+                    const uint32_t beg = __ldg(a.grid_cell_start + cell), end = __ldg(a.grid_cell_start + cell + 1);
+                    for (uint32_t k = beg; k < end && !occluded; ++k) {
+                        const int prim = __ldg(a.grid_entries + k);
+                        if (COUNT) n_tri += 1;
+                        occluded = prim_occludes(a.tris, prim, prim == self_prim, o, d, L, c);
+                    }
+                }
+                for (uint32_t k = 0; k < a.grid_n_big && !occluded; ++k) {          // primitives outside the grids (the ground)
+                    const int prim = __ldg(a.grid_big + k);
                     if (COUNT) n_tri += 1;
                     occluded = prim_occludes(a.tris, prim, prim == self_prim, o, d, L, c);
                 }
+            } else {
+                occluded = lane_anyhit_walk<COUNT>(a, o, d, L, self_prim, c, n_box, n_tri, overflow);
             }
-            for (uint32_t k = 0; k < a.grid_n_big && !occluded; ++k) {              // primitives outside the grids (the ground)
-                const int prim = __ldg(a.grid_big + k);
-                if (COUNT) n_tri += 1;
-                occluded = prim_occludes(a.tris, prim, prim == self_prim, o, d, L, c);
-            }
-        } else {
-            occluded = lane_anyhit_walk<COUNT>(a, o, d, L, self_prim, c, n_box, n_tri, overflow);
         }
-        if (occluded) atomicOr(a.masks + (size_t)it * a.mask_words + (i >> 5), 1u << (i & 31));
+        // transposed mask: one word per (block of 32 hit points, sample), bit = hit point within the block; k_shade reads
+        // bit (slot % 32) of word (slot / 32) * nls + i.  Every word is written exactly once: no atomics, no clearing.
+        const unsigned m = __ballot_sync(0xffffffffu, occluded);
+        if (lane == 0) a.masks[(size_t)blk * a.nb_light_sample + i] = m;
     }
     if (__any_sync(0xffffffffu, overflow != 0) && lane == 0) atomicAdd(a.counters + RTB_CTR_OVERFLOW, 1ull);
     if (COUNT) {
