@@ -221,7 +221,7 @@ __device__ __noinline__ bool lane_anyhit_walk(const TraceArgs& a, f3 o, f3 d, fl
             if (h1) { cur = c1; continue; }
         } else {
             if (COUNT) n_tri += 1;
-            if (prim_occludes(a.tris, ~cur, ~cur == self_prim, o, d, L, c)) return true;
+            if (prim_occludes(a.tris, ~cur, ~cur == self_prim, o, d, L, &c)) return true;
         }
         if (sp == 0) return false;
         cur = stack[--sp];
@@ -255,7 +255,6 @@ __global__ void __launch_bounds__(256) k_shadow_grid(const TraceArgs a) {
             const float4 lp = __ldg(a.light_pts + idx);
             float L; f3 d;
             normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);           // Ray::new + distance (src/main.rs:201-202)
-            const RayCull c = make_cull(o, d);
             const float4* gp = reinterpret_cast<const float4*>(a.grid_lights + idx);
             const float4 g0 = __ldg(gp), g1 = __ldg(gp + 1), g2 = __ldg(gp + 2);  // {px,py,pz,H} {x0,z0,cell,inv_cell} {nx,nz,cell_base,-}
             const float dy = g0.y - o.y;
@@ -268,17 +267,19 @@ __global__ void __launch_bounds__(256) k_shadow_grid(const TraceArgs a) {
                     const uint32_t beg = __ldg(a.grid_cell_start + cell), end = __ldg(a.grid_cell_start + cell + 1);
                     for (uint32_t k = beg; k < end && !occluded; ++k) {
                         const int prim = __ldg(a.grid_entries + k);
+                        if (prim == self_prim) continue;                         // the hit primitive: k_shade's per-ray self test
                         if (COUNT) n_tri += 1;
-                        occluded = prim_occludes(a.tris, prim, prim == self_prim, o, d, L, c);
+                        occluded = prim_occludes(a.tris, prim, false, o, d, L, nullptr);
                     }
                 }
                 for (uint32_t k = 0; k < a.grid_n_big && !occluded; ++k) {          // primitives outside the grids (the ground)
                     const int prim = __ldg(a.grid_big + k);
+                    if (prim == self_prim) continue;
                     if (COUNT) n_tri += 1;
-                    occluded = prim_occludes(a.tris, prim, prim == self_prim, o, d, L, c);
+                    occluded = prim_occludes(a.tris, prim, false, o, d, L, nullptr);
                 }
             } else {
-                occluded = lane_anyhit_walk<COUNT>(a, o, d, L, self_prim, c, n_box, n_tri, overflow);
+                occluded = lane_anyhit_walk<COUNT>(a, o, d, L, -1, make_cull(o, d), n_box, n_tri, overflow);   // -1: the hit primitive is k_shade's
             }
         }
         // transposed mask: one word per (block of 32 hit points, sample), bit = hit point within the block; k_shade reads
