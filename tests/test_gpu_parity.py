@@ -283,3 +283,49 @@ def test_chunked_wavefront_equals_single_pass(rtb, big_bunny_inputs, monkeypatch
     got_list = sc.render_pixels(pix, **kw)
     for k in ("rgb_lin", "rgb8", "hit_count", "prim0", "t0"):
         assert (got_list[k] == ref_list[k]).all(), k
+
+
+def test_list_walk_shadow_path_exact(rtb, big_bunny_inputs, oracle_big_bunny, monkeypatch):
+    """RTB200_SHADOW=lists: the candidate-list / BVH-walk shadow kernels (the path taken when the light grids do not
+    apply) against the oracle, and against the default (grid) path on a full small frame."""
+    v, c, smp = big_bunny_inputs
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=2, nb_light_sample=40)
+    ref_sc = rtb.Scene(v, c); ref_sc.set_samples(smp)
+    ref, st_ref = ref_sc.render(**kw)
+    assert st_ref["grid_cells"] > 0 and st_ref["grid_big"] == 1 and st_ref["queued_groups"] == 0     # grid path; big = the ground
+    monkeypatch.setenv("RTB200_SHADOW", "lists")
+    sc = rtb.Scene(v, c); sc.set_samples(smp)
+    got, st = sc.render(**kw)
+    assert st["grid_cells"] == 0 and st["queued_groups"] > 0
+    assert (got == ref).all()
+    for k in ("primary_hits", "shadow_rays", "shadow_occluded", "queued_hits"):
+        assert st[k] == st_ref[k], k
+    xs, ys = np.meshgrid(np.arange(800, 960, 4), np.arange(440, 700, 4))
+    pix = np.stack([xs.ravel(), ys.ravel()], 1).astype(np.uint32)
+    g = sc.render_pixels(pix)
+    o = oracle_big_bunny.render(S.WIDTH, S.HEIGHT, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix)
+    assert_same(g, o, "list/walk path")
+
+
+def test_grid_path_geometry_around_and_above_the_light(rtb, built):
+    """Light grids with primitives they cannot rasterise: triangles crossing or above the light's height go to the 'big'
+    list, hit points at or above a light point walk the BVH instead; results must still equal the oracle's."""
+    v, c = S.random_soup(120, seed=11)
+    rng = np.random.default_rng(5)
+    hi = rng.uniform(-60, 60, size=(12, 3, 3)).astype(np.float32)
+    hi[:, :, 1] = rng.uniform(250, 420, size=(12, 3)).astype(np.float32)      # around and above the light (y = 262..300)
+    hi[:, :, 2] -= 150.0
+    v = np.concatenate([hi.reshape(12, 9), v]); c = np.concatenate([rng.uniform(0.1, 1, (12, 3)).astype(np.float32), c])
+    smp = S.make_samples(5003, seed=3)
+    W, H = 160, 90
+    sc = rtb.Scene(v, c); sc.set_samples(smp)
+    frame, st = sc.render(width=W, height=H, distance=40.0, nb_ray=2, nb_light_sample=24)
+    assert st["grid_cells"] > 0 and 2 <= st["grid_big"] <= 64
+    o = O.OracleScene(v, c, True).render(W, H, smp, S.EYE, S.LOOK_AT, S.UP, 40.0, S.LIGHT, nb_ray=2, nb_light_sample=24)
+    assert (frame == o["rgb8"]).all()
+    assert st["shadow_occluded"] == o["stats"]["shadow_occluded"] and st["primary_hits"] == o["stats"]["primary_hits"]
+    # camera above the scene looking down: primary hit points on the high triangles, above some light points
+    eye, look = (0.0, 600.0, -140.0), (0.0, -100000.0, -150.0)
+    o2 = O.OracleScene(v, c, True).render(W, H, smp, eye, look, (0.0, 0.0, -1.0), 60.0, S.LIGHT, nb_ray=1, nb_light_sample=24)
+    f2, st2 = sc.render(width=W, height=H, distance=60.0, nb_ray=1, nb_light_sample=24, eye=eye, look_at=look, up=(0.0, 0.0, -1.0))
+    assert (f2 == o2["rgb8"]).all() and st2["shadow_occluded"] == o2["stats"]["shadow_occluded"]
