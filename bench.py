@@ -204,18 +204,20 @@ def main():
         dist.all_reduce(t)
         st = dict(zip(keys, [int(x) for x in t.tolist()]))
     # kernel-only time of this rank's trace kernel (events inside the library, stream of the launch)
-    kms, per_kernel = [], {"k_primary": [], "k_shadow_plan+k_shadow_queue": [], "k_shade": []}
+    kms, per_kernel = [], {"k_primary": [], "k_shadow_grid": [], "k_shade": []}
     for _ in range(3):
         flush_buf.zero_()
         torch.cuda.synchronize(dev)
         _, s1 = scene.render(width=WIDTH, height=HEIGHT, band_rows=BAND_ROWS, rank=rank, world=world, profile=True, **kw)
         kms.append(s1["kernel_ms"])
         per_kernel["k_primary"].append(s1["primary_ms"])
-        per_kernel["k_shadow_plan+k_shadow_queue"].append(s1["shadow_ms"])
+        per_kernel["k_shadow_grid"].append(s1["shadow_ms"])
         per_kernel["k_shade"].append(s1["shade_ms"])
     kernel_ms = float(np.mean(kms))
     per_kernel = {k: float(np.mean(v)) for k, v in per_kernel.items()}
-    queue = {"queued_hit_points": s1["queued_hits"], "shadow_sub_items": s1["queued_groups"]}
+    queue = {"queued_hit_points": s1["queued_hits"], "path": "light grids" if s1["grid_cells"] else "candidate lists / BVH walks",
+             "grid_cells": s1["grid_cells"], "grid_entries": s1["grid_entries"], "grid_big_primitives": s1["grid_big"],
+             "grid_build_ms_per_sample_table": s1["grid_build_ms"], "list_pairs": s1["queued_groups"]}
 
     # ---- end to end through the public C ABI with HOST buffers: per step H2D of the sample table (the reference draws
     #      a fresh table per render(), src/main.rs:260-265) + params, render, D2H of this rank's RGB8 rows; N>1: the rows
@@ -274,7 +276,7 @@ def main():
                     "path": "rtb_scene_set_samples + rtb_render with pinned host buffers"},
             "gpu_launches": args.steps * (s1["launches"] * world + (1 if world > 1 else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-                         "traffic": None, "kernel": "wavefront chain k_primary -> k_shadow_plan -> k_shadow_queue -> k_shade (one launch each per frame)",
+                         "traffic": None, "kernel": "wavefront chain k_primary -> k_shadow_grid -> k_shade per chunk of 16 Mi rays (per_kernel_ms: chunks in sequence, RTB_FLAG_PROFILE)",
                          "kernel_ms": kernel_ms, "per_kernel_ms": per_kernel, "shadow_queue": queue, "algorithmic_flops_per_launch": flops / world,
                          "peak_source": "SMs x 128 FP32 lanes x 2 x SM clock under load (%d SMs, %.0f MHz); MEASURED_PEAKS.json has no FP32 entry"
                                         % (props.multi_processor_count, sm_mhz)},
