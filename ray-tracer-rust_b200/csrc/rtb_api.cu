@@ -293,6 +293,7 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     if (s->shadow_mode != 1 && s->grid.valid && s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need) {
         a->grid_lights = s->grid.d_lights; a->grid_cell_start = s->grid.d_cell_start; a->grid_entries = s->grid.d_entries;
         a->grid_big = s->grid.d_big; a->grid_n_big = s->grid.n_big;
+        a->grid_union = s->grid.d_union; a->grid_sat = s->grid.d_sat;
     }
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
     a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;

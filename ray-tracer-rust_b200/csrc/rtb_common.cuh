@@ -54,6 +54,11 @@ struct GridLight {                 // one per light point
     uint32_t cell_base, pad;       // first cell of this grid in cell_start
 };
 
+struct GridUnion {                 // occupancy of all light grids together, as a summed-area table (k_primary's shadow-queue test)
+    float x0, z0, cell, inv_cell;
+    int nx, nz; float y_plane, pad;
+};
+
 struct GridArgs {                  // build-time arguments
     const float4* tris; uint32_t n_tris;
     const float4* light_pts; uint32_t n_lights;
@@ -65,14 +70,16 @@ struct GridArgs {                  // build-time arguments
     uint32_t* cell_fill;           // per cell count / cursor
     int* entries;
     int* big_list;
-    uint32_t* ctl;                 // [0] total cells [1] big primitives
+    uint32_t* ctl;                 // [0] total cells [1] big primitives [2] union nx [3] union nz
+    GridUnion* uni; uint32_t* sat; // union occupancy: (nz + 1) x (nx + 1) summed-area table with a zero border
     uint32_t cell_cap;
 };
 
 struct RtbGrid {                   // host-side owner of the light grids of one scene (rtb_grid.cu)
     float y_min, mean_extent; bool stats_ok;
     GridLight* d_lights; unsigned int* d_lbounds; uint32_t* d_prim_flags; uint32_t* d_cell_start; uint32_t* d_cell_fill;
-    int* d_entries; int* d_big; uint32_t* d_ctl; void* d_cub;
+    int* d_entries; int* d_big; uint32_t* d_ctl; void* d_cub; GridUnion* d_union; uint32_t* d_sat;
+    size_t union_cap, sat_cap;
     size_t lights_cap, lbounds_cap, flags_cap, cell_start_cap, cell_fill_cap, entries_cap, big_cap, ctl_cap, cub_bytes;
     bool valid; uint32_t n_lights, n_big, total_cells, total_entries; float build_ms;
     // cache key: the grids depend on the sample table and on how many of its entries the frame addresses
@@ -111,6 +118,7 @@ struct TraceArgs {
     uint32_t pool_cap;
     // light grids (rtb_grid.cu); grid_lights == nullptr: list / walk path
     const GridLight* grid_lights; const uint32_t* grid_cell_start; const int* grid_entries; const int* grid_big; uint32_t grid_n_big;
+    const GridUnion* grid_union; const uint32_t* grid_sat;
     uint32_t* masks;                     // mask_words per queued hit point: bit i = light sample i occluded
     uint32_t* queue_ctl;                 // [0] hit points queued by k_primary [1] k_shadow_plan ticket [2,3] k_shadow_queue ticket [4] walk pairs
                                          // [5] of which with an entry node [6] list pairs [7] pool entries used [8,9] k_shadow_lists ticket

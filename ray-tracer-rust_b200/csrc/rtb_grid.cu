@@ -24,6 +24,7 @@
 #define RTB_GRID_TAU 0.02f            // a point is projectable from P if P.y - y > TAU * (P.y - y_plane): magnification <= 50
 #define RTB_GRID_MAX_CELLS_PER_PRIM 4096
 #define RTB_GRID_MAX_DIM 8192
+#define RTB_GRID_UNION_DIM 2048
 
 __device__ __forceinline__ unsigned int g_f2ord(float f) { const unsigned int b = __float_as_uint(f); return (b & 0x80000000u) ? ~b : (b | 0x80000000u); }
 __device__ __forceinline__ float g_ord2f(unsigned int o) { return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o); }
@@ -134,7 +135,63 @@ __global__ void __launch_bounds__(1024) k_grid_layout(GridArgs g) {
             base += (unsigned long long)g.lights[l].nx * (unsigned long long)g.lights[l].nz;
         }
         g.ctl[0] = base > 0xffffffffull ? 0xffffffffu : (uint32_t)base;           // total cells (the host checks it against cell_cap)
+        // the union grid: covers every light grid, at most RTB_GRID_UNION_DIM cells a side
+        float ux0 = 3.0e38f, uz0 = 3.0e38f, ux1 = -3.0e38f, uz1 = -3.0e38f, cell = g.cell0;
+        for (uint32_t l = 0; l < g.n_lights; ++l) {
+            const GridLight G = g.lights[l];
+            if (G.nx <= 0) continue;
+            ux0 = fminf(ux0, G.x0); uz0 = fminf(uz0, G.z0);
+            ux1 = fmaxf(ux1, G.x0 + (float)G.nx * G.cell); uz1 = fmaxf(uz1, G.z0 + (float)G.nz * G.cell);
+            cell = fmaxf(cell, G.cell);
+        }
+        GridUnion U;
+        U.y_plane = g.y_plane; U.pad = 0.0f; U.x0 = 0.0f; U.z0 = 0.0f; U.cell = cell; U.inv_cell = 0.0f; U.nx = 0; U.nz = 0;
+        if (ux0 <= ux1) {
+            cell = fmaxf(cell, fmaxf(ux1 - ux0, uz1 - uz0) / (float)(RTB_GRID_UNION_DIM - 2));
+            U.x0 = ux0; U.z0 = uz0; U.cell = cell; U.inv_cell = 1.0f / cell;
+            U.nx = (int)ceilf((ux1 - ux0) / cell) + 1; U.nz = (int)ceilf((uz1 - uz0) / cell) + 1;
+        }
+        *g.uni = U;
+        g.ctl[2] = (uint32_t)U.nx; g.ctl[3] = (uint32_t)U.nz;
     }
+}
+
+// ---- union occupancy: which plane cells have ANY primitive in ANY light point's grid ------------------------------------
+__global__ void k_grid_union_mark(GridArgs g, uint32_t total_cells) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= total_cells || g.cell_start[c + 1] == g.cell_start[c]) return;
+    uint32_t lo = 0, hi = g.n_lights - 1;                          // the light whose grid holds cell c: last cell_base <= c
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi + 1) >> 1;
+        if (g.lights[mid].cell_base <= c) lo = mid; else hi = mid - 1;
+    }
+    while (lo > 0 && g.lights[lo].nx <= 0) --lo;                   // empty grids share their successor's base
+    const GridLight G = g.lights[lo];
+    const GridUnion U = *g.uni;
+    const uint32_t local = c - G.cell_base;
+    const int cz = (int)(local / (uint32_t)G.nx), cx = (int)(local - (uint32_t)cz * (uint32_t)G.nx);
+    const float eps = 1e-3f * G.cell;
+    int ux0 = (int)floorf((G.x0 + cx * G.cell - eps - U.x0) * U.inv_cell), ux1 = (int)floorf((G.x0 + (cx + 1) * G.cell + eps - U.x0) * U.inv_cell);
+    int uz0 = (int)floorf((G.z0 + cz * G.cell - eps - U.z0) * U.inv_cell), uz1 = (int)floorf((G.z0 + (cz + 1) * G.cell + eps - U.z0) * U.inv_cell);
+    ux0 = max(ux0, 0); uz0 = max(uz0, 0); ux1 = min(ux1, U.nx - 1); uz1 = min(uz1, U.nz - 1);
+    const uint32_t W = (uint32_t)U.nx + 1;
+    for (int z = uz0; z <= uz1; ++z)
+        for (int x = ux0; x <= ux1; ++x) g.sat[(uint32_t)(z + 1) * W + (uint32_t)(x + 1)] = 1u;
+}
+
+__global__ void k_grid_sat_rows(uint32_t* __restrict__ sat, int nx, int nz) {     // one thread per row
+    const int z = blockIdx.x * blockDim.x + threadIdx.x;
+    if (z >= nz) return;
+    uint32_t* row = sat + (size_t)(z + 1) * (nx + 1);
+    uint32_t acc = 0;
+    for (int x = 1; x <= nx; ++x) { acc += row[x]; row[x] = acc; }
+}
+
+__global__ void k_grid_sat_cols(uint32_t* __restrict__ sat, int nx, int nz) {     // one thread per column
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= nx) return;
+    uint32_t acc = 0;
+    for (int z = 1; z <= nz; ++z) { uint32_t* p = sat + (size_t)z * (nx + 1) + (x + 1); acc += *p; *p = acc; }
 }
 
 // ---- passes C / D: conservative rasterisation of every projected primitive into its light point's grid -----------------
@@ -349,7 +406,7 @@ cudaError_t rtb_grid_scene_stats(RtbGrid& G, const float4* d_tris, uint32_t n, c
 
 void rtb_grid_free(RtbGrid& G) {
     cudaFree(G.d_lights); cudaFree(G.d_lbounds); cudaFree(G.d_prim_flags); cudaFree(G.d_cell_start); cudaFree(G.d_cell_fill);
-    cudaFree(G.d_entries); cudaFree(G.d_big); cudaFree(G.d_ctl); cudaFree(G.d_cub);
+    cudaFree(G.d_entries); cudaFree(G.d_big); cudaFree(G.d_ctl); cudaFree(G.d_cub); cudaFree(G.d_union); cudaFree(G.d_sat);
     memset(&G, 0, sizeof(G));
 }
 
@@ -369,12 +426,13 @@ cudaError_t rtb_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, co
     GRID_CK(grid_reserve(&G.d_prim_flags, &G.flags_cap, (size_t)n_tris));
     GRID_CK(grid_reserve(&G.d_big, &G.big_cap, (size_t)RTB_GRID_MAX_BIG));
     GRID_CK(grid_reserve(&G.d_ctl, &G.ctl_cap, (size_t)4));
+    GRID_CK(grid_reserve(&G.d_union, &G.union_cap, (size_t)1));
     GridArgs g; memset(&g, 0, sizeof(g));
     g.tris = d_tris; g.n_tris = n_tris; g.light_pts = d_light_pts; g.n_lights = n_lights;
     // the plane sits a little below the lowest vertex so that ground-level origins project with a finite scale
     g.y_plane = G.y_min - 1.0f - 1e-3f * fabsf(G.y_min);
     g.cell0 = G.mean_extent * cell_factor;
-    g.lights = G.d_lights; g.lbounds = G.d_lbounds; g.prim_flags = G.d_prim_flags; g.big_list = G.d_big; g.ctl = G.d_ctl;
+    g.lights = G.d_lights; g.lbounds = G.d_lbounds; g.prim_flags = G.d_prim_flags; g.big_list = G.d_big; g.ctl = G.d_ctl; g.uni = G.d_union;
     g.cell_cap = (uint32_t)CELL_CAP;
     const unsigned nmax = n_lights > n_tris ? n_lights : n_tris;
     k_grid_init<<<(nmax + 255) / 256, 256, 0, st>>>(G.d_lbounds, n_lights, G.d_prim_flags, n_tris, G.d_ctl);
@@ -409,6 +467,19 @@ cudaError_t rtb_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, co
     GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
     k_grid_raster<true><<<gw, 256, 0, st>>>(g);
     GRID_CK(cudaGetLastError());
+    {   // union occupancy + summed-area table
+        const int unx = (int)h_ctl[2], unz = (int)h_ctl[3];
+        const size_t ns = (size_t)(unx + 1) * (size_t)(unz + 1);
+        GRID_CK(grid_reserve(&G.d_sat, &G.sat_cap, ns));
+        g.sat = G.d_sat;
+        GRID_CK(cudaMemsetAsync(G.d_sat, 0, ns * sizeof(uint32_t), st));
+        if (G.total_cells) k_grid_union_mark<<<(G.total_cells + 255) / 256, 256, 0, st>>>(g, G.total_cells);
+        if (unx > 0 && unz > 0) {
+            k_grid_sat_rows<<<(unz + 127) / 128, 128, 0, st>>>(G.d_sat, unx, unz);
+            k_grid_sat_cols<<<(unx + 127) / 128, 128, 0, st>>>(G.d_sat, unx, unz);
+        }
+        GRID_CK(cudaGetLastError());
+    }
     GRID_CK(cudaEventRecord(ev1, st));
     GRID_CK(cudaEventSynchronize(ev1));
     GRID_CK(cudaEventElapsedTime(&G.build_ms, ev0, ev1));

@@ -9,7 +9,8 @@ for spec in "$@"; do
   name="${spec%%:*}"; flags="${spec#*:}"
   $NV $flags -Xptxas -v -c csrc/rtb_trace.cu -o build/rtb_trace_$name.o 2> build/rtb_trace_$name.log &
   $NV $flags -c csrc/rtb_api.cu -o build/rtb_api_$name.o &
+  $NV $flags -c csrc/rtb_grid.cu -o build/rtb_grid_$name.o &
   wait
-  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/librtb200_$name.so build/rtb_api_$name.o build/rtb_trace_$name.o build/rtb_bvh.o build/rtb_refpair.o build/rtb_host.o -cudart shared
+  nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/librtb200_$name.so build/rtb_api_$name.o build/rtb_trace_$name.o build/rtb_grid_$name.o build/rtb_bvh.o build/rtb_refpair.o build/rtb_host.o -cudart shared
   echo "$name: $(grep -A2 'Compiling entry function .*ILb0' build/rtb_trace_$name.log | grep -o 'Function[^:]*\|Used [0-9]* registers' | tr '\n' ' ')"
 done
