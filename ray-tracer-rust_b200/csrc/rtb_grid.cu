@@ -230,6 +230,7 @@ __global__ void k_grid_raster(GridArgs g) {
     for (int cz = cz0; cz <= cz1; ++cz) {
         const float rz0 = G.z0 + cz * G.cell - m, rz1 = G.z0 + (cz + 1) * G.cell + m;
         for (int cx = cx0; cx <= cx1; ++cx) {
+            bool covers = true;
             if (use_edges) {
                 const float rx0 = G.x0 + cx * G.cell - m, rx1 = G.x0 + (cx + 1) * G.cell + m;
                 bool out = false;
@@ -241,12 +242,27 @@ __global__ void k_grid_raster(GridArgs g) {
                     // rounding of e: a few ulps of the terms; keep the cell unless it is outside by more than that
                     const float tol = 4e-6f * (fabsf(ex[k] * fx) + fabsf(ez[k] * fz) + fabsf(ec[k]));
                     out = out || (e < -tol);
+                    if (FILL) {                                                 // the corner least far along it: inside -> the cell is covered
+                        const float gx = ex[k] >= 0.0f ? rx0 : rx1, gz = ez[k] >= 0.0f ? rz0 : rz1;
+                        covers = covers && (ex[k] * gx + ez[k] * gz + ec[k] > tol);
+                    }
                 }
                 if (out) continue;
             }
             const uint32_t cell = G.cell_base + (uint32_t)cz * (uint32_t)G.nx + (uint32_t)cx;
-            if (FILL) g.entries[g.cell_start[cell] + atomicAdd(g.cell_fill + cell, 1u)] = (int)prim;
-            else atomicAdd(g.cell_fill + cell, 1u);
+            if (FILL) {
+                // Order within a cell (a heuristic, any order is correct): primitives whose projection covers the whole
+                // cell go to the front, the others to the back -- a ray that reads the cell is then usually occluded by
+                // the first or second primitive it tests.  One counter, front count in the low and back count in the
+                // high half (cells with >= 2^16 entries are filled front to back only).
+                const uint32_t beg = g.cell_start[cell], cnt = g.cell_start[cell + 1] - beg;
+                uint32_t pos;
+                if (cnt >= 65536u || (use_edges && covers)) pos = beg + (atomicAdd(g.cell_fill + cell, 1u) & (cnt >= 65536u ? 0xffffffffu : 0xffffu));
+                else pos = beg + cnt - 1u - (atomicAdd(g.cell_fill + cell, 0x10000u) >> 16);
+                g.entries[pos] = (int)prim;
+            } else {
+                atomicAdd(g.cell_fill + cell, 1u);
+            }
         }
     }
 }
@@ -285,64 +301,192 @@ __device__ __noinline__ bool lane_anyhit_walk(const TraceArgs& a, f3 o, f3 d, fl
     }
 }
 
-// One lane per ray (queued hit point, light sample i).  32 consecutive rays = 32 consecutive queue slots (a pixel tile
-// of k_primary) with the SAME sample, hence normally the same light point: the lanes read neighbouring cells of one grid.
+// A warp takes a ticket = (block of 32 consecutive queue slots, RTB_GRID_R consecutive light samples): lane l owns the
+// R rays of hit point l.  32 consecutive slots are a pixel tile of k_primary and a sample index means the same light
+// point for (nearly) all of them, so the lanes read neighbouring cells of one grid.
+//
+// The candidate lists differ in length (most rays of a tile near a shadow edge have none, a few have several) and a ray
+// stops at its first occluder, so a loop per lane leaves two thirds of the lanes idle (ncu, profiles/r1c: 11.8 of 32
+// threads per instruction).  The tests are therefore dealt out anew every round: the A rays that still have candidates
+// and no occluder offer their next `share` candidates (share = 1 when A >= 17, else the power of two <= 32 / A), lane j
+// tests candidate j % share of the (j / share)-th such ray -- its origin, direction and cursor come from shared memory --
+// and the verdicts return with one warp-wide OR per sample.  Only the first half of the test (prim_mt_q) runs in the
+// rounds; a ray that passes it stops offering candidates, and the second half (prim_confirm_q: the leaf box and the
+// distance compare, which hardly ever reject) runs afterwards in the ray's own lane.  If it does reject, the ray walks
+// the rest of its list alone.  Which lane evaluates a (ray, primitive) pair never changes its value.
 // Result: the transposed occlusion masks described at the end of the loop.
+#ifndef RTB_GRID_R
+#define RTB_GRID_R 2
+#endif
 template <bool COUNT>
 __global__ void __launch_bounds__(256) k_shadow_grid(const TraceArgs a) {
-    const uint32_t lane = threadIdx.x & 31;
+    constexpr int R = RTB_GRID_R;
+    __shared__ float4 s_o[8][32];                        // {o, self primitive}
+    __shared__ float4 s_d[8][R][32];                     // {d, L}
+    __shared__ uint32_t s_cur[8][R][32], s_take[8][R][32];   // next entry (index into grid_entries), entries offered this round
+    __shared__ uint32_t s_src[8][32];                    // rank among the active rays -> r * 32 + lane
+    __shared__ uint2 s_tent[8][R][32];                   // a candidate that passed prim_mt_q: {primitive, t}
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, lt = (1u << lane) - 1u;
     const uint32_t n_items = a.queue_ctl[0];
-    const uint32_t total = ((n_items + 31) / 32) * a.nb_light_sample;          // tickets: (block of 32 hit points, sample i)
+    const uint32_t groups = (a.nb_light_sample + R - 1) / R;
+    const uint32_t total = ((n_items + 31) / 32) * groups;
     uint32_t n_box = 0, n_tri = 0, overflow = 0;
     for (;;) {
         uint32_t tk = 0;
         if (lane == 0) tk = atomicAdd(a.queue_ctl + 8, 1u);
         tk = __shfl_sync(0xffffffffu, tk, 0);
         if (tk >= total) break;
-        const uint32_t blk = tk / a.nb_light_sample, i = tk - blk * a.nb_light_sample;
+        const uint32_t blk = tk / groups, i0 = (tk - blk * groups) * R;
         const uint32_t it = blk * 32 + lane;
-        bool occluded = false;
+        uint32_t cur[R], rem[R];
+        uint32_t occ = 0, walk = 0, below = 0, tent = 0;            // bit r: ray r of this lane
+        int self_prim = -1;
+        f3 o = mk3(0.0f, 0.0f, 0.0f);
+#pragma unroll
+        for (int r = 0; r < R; ++r) { cur[r] = 0; rem[r] = 0; }
         if (it < n_items) {
             const float4* ip = a.items + RTB_ITEM_F4 * (size_t)it;
-            const float4 i0 = __ldg(ip), i1 = __ldg(ip + 1);
-            const int self_prim = (int)(__float_as_uint(i0.y) & RTB_PRIM_MASK);
-            const f3 o = mk3(i1.x, i1.y, i1.z);
-            uint32_t idx = __float_as_uint(i0.w) + i;                            // (r*NB_RAY + i) % len, src/main.rs:194
-            if (idx >= a.n_samples) idx %= a.n_samples;
-            const float4 lp = __ldg(a.light_pts + idx);
-            float L; f3 d;
-            normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);           // Ray::new + distance (src/main.rs:201-202)
-            const float4* gp = reinterpret_cast<const float4*>(a.grid_lights + idx);
-            const float4 g0 = __ldg(gp), g1 = __ldg(gp + 1), g2 = __ldg(gp + 2);  // {px,py,pz,H} {x0,z0,cell,inv_cell} {nx,nz,cell_base,-}
-            const float dy = g0.y - o.y;
-            if (dy > RTB_GRID_TAU * g0.w) {
-                const float s = g0.w / dy;
-                const float fx = (fmaf(o.x - g0.x, s, g0.x) - g1.x) * g1.w, fz = (fmaf(o.z - g0.z, s, g0.z) - g1.y) * g1.w;
-                const int nx = __float_as_int(g2.x), nz = __float_as_int(g2.y);
-                if (fx >= 0.0f && fz >= 0.0f && fx < (float)nx && fz < (float)nz) {   // false for NaN
-                    const uint32_t cell = __float_as_uint(g2.z) + (uint32_t)fz * (uint32_t)nx + (uint32_t)fx;
-                    const uint32_t beg = __ldg(a.grid_cell_start + cell), end = __ldg(a.grid_cell_start + cell + 1);
-                    for (uint32_t k = beg; k < end && !occluded; ++k) {
-                        const int prim = __ldg(a.grid_entries + k);
-                        if (prim == self_prim) continue;                         // the hit primitive: k_shade's per-ray self test
-                        if (COUNT) n_tri += 1;
-                        occluded = prim_occludes(a.tris, prim, false, o, d, L, nullptr);
+            const float4 it0 = __ldg(ip), it1 = __ldg(ip + 1);
+            self_prim = (int)(__float_as_uint(it0.y) & RTB_PRIM_MASK);
+            o = mk3(it1.x, it1.y, it1.z);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (i0 + r >= a.nb_light_sample) continue;
+                uint32_t idx = __float_as_uint(it0.w) + i0 + r;                  // (r*NB_RAY + i) % len, src/main.rs:194
+                if (idx >= a.n_samples) idx %= a.n_samples;
+                const float4 lp = __ldg(a.light_pts + idx);
+                float L; f3 d;
+                normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);           // Ray::new + distance (src/main.rs:201-202)
+                s_d[w][r][lane] = make_float4(d.x, d.y, d.z, L);
+                const float4* gp = reinterpret_cast<const float4*>(a.grid_lights + idx);
+                const float4 g0 = __ldg(gp), g1 = __ldg(gp + 1), g2 = __ldg(gp + 2);  // {px,py,pz,H} {x0,z0,cell,inv_cell} {nx,nz,cell_base,-}
+                const float dy = g0.y - o.y;
+                if (dy > RTB_GRID_TAU * g0.w) {                                   // hence d.y = rn(dy / L) >= +0
+                    below |= 1u << r;
+                    const float s = g0.w / dy;
+                    const float fx = (fmaf(o.x - g0.x, s, g0.x) - g1.x) * g1.w, fz = (fmaf(o.z - g0.z, s, g0.z) - g1.y) * g1.w;
+                    const int nx = __float_as_int(g2.x), nz = __float_as_int(g2.y);
+                    if (fx >= 0.0f && fz >= 0.0f && fx < (float)nx && fz < (float)nz) {   // false for NaN
+                        const uint32_t cell = __float_as_uint(g2.z) + (uint32_t)fz * (uint32_t)nx + (uint32_t)fx;
+                        cur[r] = __ldg(a.grid_cell_start + cell);
+                        rem[r] = __ldg(a.grid_cell_start + cell + 1) - cur[r];
+                    }
+                } else {
+                    walk |= 1u << r;
+                }
+            }
+        }
+        s_o[w][lane] = make_float4(o.x, o.y, o.z, __int_as_float(self_prim));
+        if (COUNT) {
+            uint32_t nz_ = 0, sum_ = 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) { nz_ += rem[r] > 0; sum_ += rem[r]; }
+            for (int off_ = 16; off_ > 0; off_ >>= 1) { sum_ += __shfl_down_sync(0xffffffffu, sum_, off_); nz_ += __shfl_down_sync(0xffffffffu, nz_, off_); }
+            if (lane == 0) { atomicAdd(a.counters + 12, 1ull); atomicAdd(a.counters + 13, (unsigned long long)sum_); atomicAdd(a.counters + 14, (unsigned long long)nz_); }
+        }
+        for (;;) {
+            unsigned act[R]; uint32_t base[R + 1];
+            base[0] = 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                act[r] = __ballot_sync(0xffffffffu, rem[r] > 0 && !((tent >> r) & 1u));
+                base[r + 1] = base[r] + __popc(act[r]);
+            }
+            const uint32_t A = base[R];
+            if (!A) break;
+            const uint32_t sh = A > 16 ? 0u : A > 8 ? 1u : A > 4 ? 2u : A > 2 ? 3u : A > 1 ? 4u : 5u;     // share = 1 << sh
+            uint32_t served = 0;                                      // bit r: ray r of this lane is dealt out this round
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if ((act[r] >> lane) & 1u) {
+                    const uint32_t rk = base[r] + __popc(act[r] & lt);
+                    if (rk < 32u) {
+                        served |= 1u << r;
+                        s_src[w][rk] = (uint32_t)r * 32u + lane;
+                        s_cur[w][r][lane] = cur[r];
+                        s_take[w][r][lane] = min(rem[r], 1u << sh);
                     }
                 }
+            }
+            __syncwarp();
+            const uint32_t rank = lane >> sh, off = lane & ((1u << sh) - 1u);
+            bool hit = false; uint32_t src = 0; int my_prim = -1; float my_t = 0.0f;
+            if (rank < A) {
+                src = s_src[w][rank];
+                const uint32_t sr = src >> 5, sl = src & 31u;
+                if (off < s_take[w][sr][sl]) {
+                    const int prim = __ldg(a.grid_entries + s_cur[w][sr][sl] + off);
+                    const float4 ro = s_o[w][sl];
+                    if (prim != __float_as_int(ro.w)) {                              // the hit primitive: k_shade's per-ray self test
+                        const float4 q0 = __ldg(a.tris + 3 * prim), q1 = __ldg(a.tris + 3 * prim + 1), q2 = __ldg(a.tris + 3 * prim + 2);
+                        const f3 po = mk3(ro.x, ro.y, ro.z);
+                        if (!prim_below_origin(q0, q1, q2, po)) {
+                            const float4 rd = s_d[w][sr][sl];
+                            float t;
+                            if (COUNT) n_tri += 1;
+                            hit = prim_mt_q(q0, q1, q2, po, mk3(rd.x, rd.y, rd.z), t);
+                            if (hit) { s_tent[w][sr][sl].x = (uint32_t)prim; my_prim = prim; my_t = t; }   // several lanes may: one wins
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (hit && s_tent[w][src >> 5][src & 31u].x == (uint32_t)my_prim) s_tent[w][src >> 5][src & 31u].y = __float_as_uint(my_t);   // a cell lists a primitive once
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const unsigned verdict = __reduce_or_sync(0xffffffffu, (hit && (src >> 5) == (uint32_t)r) ? (1u << (src & 31u)) : 0u);
+                if ((served >> r) & 1u) {
+                    if ((verdict >> lane) & 1u) tent |= 1u << r;         // cur[r] stays at the start of this round (see below)
+                    else { const uint32_t take = min(rem[r], 1u << sh); cur[r] += take; rem[r] -= take; }
+                }
+            }
+            if (COUNT) {
+                const unsigned hits_ = __ballot_sync(0xffffffffu, hit);
+                if (lane == 0) { atomicAdd(a.counters + 6, 1ull); atomicAdd(a.counters + 7, (unsigned long long)A); atomicAdd(a.counters + 15, (unsigned long long)__popc(hits_)); }
+            }
+            __syncwarp();
+        }
+        // second half of the test for the rays that found a candidate, in their own lane; then what the grids do not cover
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool valid = it < n_items && i0 + r < a.nb_light_sample;
+            const float4 rd = s_d[w][r][lane];
+            const f3 d = mk3(rd.x, rd.y, rd.z);
+            const float L = rd.w;
+            bool occluded = false;
+            if ((tent >> r) & 1u) {
+                const uint2 tp = s_tent[w][r][lane];
+                const int prim = (int)tp.x;
+                occluded = prim_confirm_q(__ldg(a.tris + 3 * prim), __ldg(a.tris + 3 * prim + 1), __ldg(a.tris + 3 * prim + 2), o, d, L, __uint_as_float(tp.y));
+                for (uint32_t k = 0; k < rem[r] && !occluded; ++k) {              // rejected after all: the rest of the list, from the round's start
+                    const int p2 = __ldg(a.grid_entries + cur[r] + k);
+                    if (p2 == self_prim) continue;
+                    if (COUNT) n_tri += 1;
+                    occluded = prim_occludes(a.tris, p2, false, o, d, L, nullptr);
+                }
+            }
+            if (valid && ((below >> r) & 1u)) {
                 for (uint32_t k = 0; k < a.grid_n_big && !occluded; ++k) {          // primitives outside the grids (the ground)
                     const int prim = __ldg(a.grid_big + k);
                     if (prim == self_prim) continue;
+                    const float4 q0 = __ldg(a.tris + 3 * prim), q1 = __ldg(a.tris + 3 * prim + 1), q2 = __ldg(a.tris + 3 * prim + 2);
+                    if (prim_below_origin(q0, q1, q2, o)) continue;
                     if (COUNT) n_tri += 1;
-                    occluded = prim_occludes(a.tris, prim, false, o, d, L, nullptr);
+                    float t;
+                    occluded = prim_mt_q(q0, q1, q2, o, d, t) && prim_confirm_q(q0, q1, q2, o, d, L, t);
                 }
-            } else {
-                occluded = lane_anyhit_walk<COUNT>(a, o, d, L, -1, make_cull(o, d), n_box, n_tri, overflow);   // -1: the hit primitive is k_shade's
             }
+            if ((walk >> r) & 1u) occluded = lane_anyhit_walk<COUNT>(a, o, d, L, -1, make_cull(o, d), n_box, n_tri, overflow);   // -1: the hit primitive is k_shade's
+            if (occluded) occ |= 1u << r;
         }
         // transposed mask: one word per (block of 32 hit points, sample), bit = hit point within the block; k_shade reads
         // bit (slot % 32) of word (slot / 32) * nls + i.  Every word is written exactly once: no atomics, no clearing.
-        const unsigned m = __ballot_sync(0xffffffffu, occluded);
-        if (lane == 0) a.masks[(size_t)blk * a.nb_light_sample + i] = m;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const unsigned m = __ballot_sync(0xffffffffu, (occ >> r) & 1u);
+            if (lane == 0 && i0 + r < a.nb_light_sample) a.masks[(size_t)blk * a.nb_light_sample + i0 + r] = m;
+        }
+        __syncwarp();
     }
     if (__any_sync(0xffffffffu, overflow != 0) && lane == 0) atomicAdd(a.counters + RTB_CTR_OVERFLOW, 1ull);
     if (COUNT) {
