@@ -47,6 +47,7 @@ struct rtb_scene {
     uint16_t* d_light_perm; size_t light_perm_cap;
     float* d_light_gbox; size_t light_gbox_cap;
     unsigned long long* d_counters;
+    bool trace_chunks;                           // RTB200_TRACE_CHUNKS=1: per-chunk kernel times of profiled renders on stderr
     float* d_light_box;                          // 6 floats, bounds of d_light_pts (k_light_bounds)
     uint8_t* d_frame; size_t frame_cap;          // staging for rtb_render (host output)
     // wavefront buffers, grown on demand and kept (see rtb_trace.cu)
@@ -177,6 +178,7 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     if (const char* env = getenv("RTB200_CHUNK_RAYS")) { const long long v = atoll(env); if (v > 0) s->chunk_rays = (uint64_t)v; }
     s->shadow_mode = 0; s->grid_cell_factor = 0.25f;
     if (const char* env = getenv("RTB200_SHADOW")) s->shadow_mode = !strcmp(env, "lists") ? 1 : (!strcmp(env, "grid") ? 2 : 0);
+    if (const char* env = getenv("RTB200_TRACE_CHUNKS")) s->trace_chunks = atoi(env) != 0;
     if (const char* env = getenv("RTB200_GRID_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->grid_cell_factor = v; }
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
@@ -251,7 +253,7 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     if (need > s->n_samples) need = s->n_samples;
     if (need > s->light_pts_cap) {
         cudaFree(s->d_light_pts); s->d_light_pts = nullptr; s->light_pts_cap = 0;
-        CUDA_TRY(cudaMalloc(&s->d_light_pts, (size_t)need * sizeof(float4)));
+        CUDA_TRY(cudaMalloc(&s->d_light_pts, (size_t)need * 3 * sizeof(float4)));      // points + pair table (k_light_pairs)
         s->light_pts_cap = (uint32_t)need;
     }
     CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
@@ -287,7 +289,7 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
     memset(a, 0, sizeof(*a));
-    a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_box = s->d_light_box;
+    a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_pairs = s->d_light_pts + need; a->light_box = s->d_light_box;
     a->light_perm = use_perm ? s->d_light_perm : nullptr;
     a->light_gbox = s->d_light_gbox; a->n_groups = n_groups; a->group_size = group_size;
     if (s->shadow_mode != 1 && s->grid.valid && s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need) {
@@ -414,6 +416,7 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
             float t = 0.0f;
             CUDA_TRY(cudaEventElapsedTime(&t, s->evp[4 * c + k], s->evp[4 * c + k + 1]));
             k_ms[k] += t;
+            if (s->trace_chunks) fprintf(stderr, "rtb200: chunk %u %s %.3f ms\n", c, k == 0 ? "primary" : k == 1 ? "shadow" : "shade", t);
         }
     }
     if (st) {

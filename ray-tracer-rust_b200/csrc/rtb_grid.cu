@@ -315,6 +315,9 @@ __device__ __noinline__ bool lane_anyhit_walk(const TraceArgs& a, f3 o, f3 d, fl
 // distance compare, which hardly ever reject) runs afterwards in the ray's own lane.  If it does reject, the ray walks
 // the rest of its list alone.  Which lane evaluates a (ray, primitive) pair never changes its value.
 // Result: the transposed occlusion masks described at the end of the loop.
+#ifndef RTB_DIAG_GRID
+#define RTB_DIAG_GRID 0      // 1: round statistics in counters 6, 7, 12-15 (scripts/diag_grid.py)
+#endif
 #ifndef RTB_GRID_R
 #define RTB_GRID_R 2
 #endif
@@ -377,7 +380,7 @@ __global__ void __launch_bounds__(256) k_shadow_grid(const TraceArgs a) {
             }
         }
         s_o[w][lane] = make_float4(o.x, o.y, o.z, __int_as_float(self_prim));
-        if (COUNT) {
+        if (COUNT && RTB_DIAG_GRID) {
             uint32_t nz_ = 0, sum_ = 0;
 #pragma unroll
             for (int r = 0; r < R; ++r) { nz_ += rem[r] > 0; sum_ += rem[r]; }
@@ -440,7 +443,7 @@ __global__ void __launch_bounds__(256) k_shadow_grid(const TraceArgs a) {
                     else { const uint32_t take = min(rem[r], 1u << sh); cur[r] += take; rem[r] -= take; }
                 }
             }
-            if (COUNT) {
+            if (COUNT && RTB_DIAG_GRID) {
                 const unsigned hits_ = __ballot_sync(0xffffffffu, hit);
                 if (lane == 0) { atomicAdd(a.counters + 6, 1ull); atomicAdd(a.counters + 7, (unsigned long long)A); atomicAdd(a.counters + 15, (unsigned long long)__popc(hits_)); }
             }
