@@ -72,13 +72,26 @@ __global__ void k_grid_classify(GridArgs g) {
     const bool ok = H > 0.0f && grid_project(P.x, P.y, P.z, H, mk3(q0.x, q0.y, q0.z), x[0], z[0]) &&
                     grid_project(P.x, P.y, P.z, H, mk3(q1.x, q1.y, q1.z), x[1], z[1]) &&
                     grid_project(P.x, P.y, P.z, H, mk3(q2.x, q2.y, q2.z), x[2], z[2]);
-    if (!ok) { atomicOr(g.prim_flags + prim, 1u); return; }
-    const float x0 = fminf(fminf(x[0], x[1]), x[2]), x1 = fmaxf(fmaxf(x[0], x[1]), x[2]);
-    const float z0 = fminf(fminf(z[0], z[1]), z[2]), z1 = fmaxf(fmaxf(z[0], z[1]), z[2]);
-    const float cells = ((x1 - x0) / g.cell0 + 2.0f) * ((z1 - z0) / g.cell0 + 2.0f);
-    if (!(cells <= (float)RTB_GRID_MAX_CELLS_PER_PRIM)) { atomicOr(g.prim_flags + prim, 1u); return; }
-    unsigned int* b = g.lbounds + 4 * light;
-    atomicMin(b + 0, g_f2ord(x0)); atomicMin(b + 1, g_f2ord(z0)); atomicMax(b + 2, g_f2ord(x1)); atomicMax(b + 3, g_f2ord(z1));
+    bool in = ok;
+    unsigned int ox0 = 0xffffffffu, oz0 = 0xffffffffu, ox1 = 0u, oz1 = 0u;
+    if (ok) {
+        const float x0 = fminf(fminf(x[0], x[1]), x[2]), x1 = fmaxf(fmaxf(x[0], x[1]), x[2]);
+        const float z0 = fminf(fminf(z[0], z[1]), z[2]), z1 = fmaxf(fmaxf(z[0], z[1]), z[2]);
+        const float cells = ((x1 - x0) / g.cell0 + 2.0f) * ((z1 - z0) / g.cell0 + 2.0f);
+        in = cells <= (float)RTB_GRID_MAX_CELLS_PER_PRIM;                              // false for NaN
+        if (in) { ox0 = g_f2ord(x0); oz0 = g_f2ord(z0); ox1 = g_f2ord(x1); oz1 = g_f2ord(z1); }
+    }
+    if (!in) atomicOr(g.prim_flags + prim, 1u);
+    // one atomic per (warp, light) instead of one per thread: the lanes of a warp are consecutive primitives of (nearly
+    // always) one light point, and every thread of a light point updates the same four words
+    const unsigned active = __activemask();
+    const unsigned peers = __match_any_sync(active, light);
+    ox0 = __reduce_min_sync(peers, ox0); oz0 = __reduce_min_sync(peers, oz0);
+    ox1 = __reduce_max_sync(peers, ox1); oz1 = __reduce_max_sync(peers, oz1);
+    if ((threadIdx.x & 31) == (unsigned)(__ffs(peers) - 1) && ox0 <= ox1) {
+        unsigned int* b = g.lbounds + 4 * light;
+        atomicMin(b + 0, ox0); atomicMin(b + 1, oz0); atomicMax(b + 2, ox1); atomicMax(b + 3, oz1);
+    }
 }
 
 __global__ void k_grid_biglist(GridArgs g) {
