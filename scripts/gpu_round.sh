@@ -1,5 +1,6 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, bench line, ncu launch list of the bench, ncu --set full of the trace kernel.
+# One gpurun call: GPU parity tests, the bench line, and the ncu launch list of the bench (one ncu per call).
+# The full capture of one kernel is a second call: scripts/gpu_profile.sh <kernel regex> <launch to skip to>.
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
@@ -7,9 +8,6 @@ tail -3 gpurun_out/pytest_gpu.log
 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 tail -1 gpurun_out/bench.json
 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
-python scripts/profile_frame.py 3840 2160 4 3 > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:k_shadow_lists -s 2 -c 1 -f -o gpurun_out/prof_trace \
-    python scripts/profile_frame.py 3840 2160 4 3 > gpurun_out/ncu_full.log 2>&1
 echo done
