@@ -425,7 +425,7 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
         st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
         st->kernel_ms = ms;
         const bool grid = s->shadow_mode != 1 && s->grid.valid;
-        st->launches = 3 + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? (grid ? 1 : 3) : 0));   // light table, bounds, groups + per chunk
+        st->launches = 4 + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? (grid ? 1 : 3) : 0));   // light table, pairs, bounds, groups + per chunk
         st->grid_cells = grid ? s->grid.total_cells : 0; st->grid_entries = grid ? s->grid.total_entries : 0;
         st->grid_big = grid ? s->grid.n_big : 0; st->grid_build_ms = grid ? s->grid.build_ms : 0.0f;
         st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];
