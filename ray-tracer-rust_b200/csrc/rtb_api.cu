@@ -18,6 +18,7 @@ cudaError_t rtb_tie_rank_device(const float4* d_tris, uint32_t n, int* d_rank_ou
 cudaError_t rtb_launch_trace(const TraceArgs&, bool, cudaStream_t, cudaEvent_t*);
 cudaError_t rtb_grid_scene_stats(RtbGrid&, const float4*, uint32_t, cudaStream_t);
 cudaError_t rtb_grid_build(RtbGrid&, const float4*, uint32_t, const float4*, uint32_t, float, cudaStream_t);
+cudaError_t rtb_cam_grid_build(RtbGrid&, const float4*, uint32_t, float4*, float4*, const CameraBasis&, float, cudaStream_t);
 void rtb_grid_free(RtbGrid&);
 cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, float*, cudaStream_t);
 cudaError_t rtb_launch_light_groups(const float4*, const float*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint16_t*, float*, cudaStream_t);
@@ -69,6 +70,10 @@ struct rtb_scene {
     uint64_t samples_version;
     int shadow_mode;                             // RTB200_SHADOW: 0 auto (grid when applicable), 1 lists/walk only, 2 grid (same as auto)
     float grid_cell_factor;                      // RTB200_GRID_CELL: cell size / log-mean primitive extent
+    // camera grid (rtb_grid.cu): the light-grid structure with the eye as projection centre, for primary rays
+    RtbGrid cam_grid; float4* d_cam_tris; float4* d_cam_origin; CameraBasis cam_key; bool cam_key_set;
+    int primary_mode;                            // RTB200_PRIMARY: 0 auto (camera grid when it applies), 1 bvh
+    float cam_cell_px;                           // RTB200_CAM_CELL: camera-grid cell size in pixels
 };
 
 // ---- Color::to_rgba threshold table (color.rs:10-33) ---------------------------------------
@@ -139,7 +144,7 @@ void rtb_scene_destroy(rtb_scene* s) {
         if (s->ev_join[k]) cudaEventDestroy(s->ev_join[k]);
     }
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
-    rtb_grid_free(s->grid);
+    rtb_grid_free(s->grid); rtb_grid_free(s->cam_grid); cudaFree(s->d_cam_tris); cudaFree(s->d_cam_origin);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -179,6 +184,9 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     s->shadow_mode = 0; s->grid_cell_factor = 0.25f;
     if (const char* env = getenv("RTB200_SHADOW")) s->shadow_mode = !strcmp(env, "lists") ? 1 : (!strcmp(env, "grid") ? 2 : 0);
     if (const char* env = getenv("RTB200_TRACE_CHUNKS")) s->trace_chunks = atoi(env) != 0;
+    s->cam_cell_px = 2.0f;
+    if (const char* env = getenv("RTB200_CAM_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->cam_cell_px = v; }
+    if (const char* env = getenv("RTB200_PRIMARY")) s->primary_mode = strcmp(env, "bvh") == 0 ? 1 : 0;
     if (const char* env = getenv("RTB200_GRID_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->grid_cell_factor = v; }
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
@@ -302,6 +310,19 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;
     a->owned_rows = rtb_owned_rows(p->height, a->band_rows, a->rank, world);
     a->cam = make_camera(p);
+    // camera grid: cached until the camera changes (a full frame only; a pixel list is too small to pay for the build)
+    if (s->primary_mode != 1 && p->nb_ray && s->n_tris) {
+        if (!(s->cam_key_set && memcmp(&s->cam_key, &a->cam, sizeof(CameraBasis)) == 0)) {
+            if (!s->d_cam_tris) CUDA_TRY(cudaMalloc(&s->d_cam_tris, (size_t)s->n_tris * 3 * sizeof(float4)));
+            if (!s->d_cam_origin) CUDA_TRY(cudaMalloc(&s->d_cam_origin, sizeof(float4)));
+            CUDA_TRY(rtb_cam_grid_build(s->cam_grid, s->d_tris, s->n_tris, s->d_cam_tris, s->d_cam_origin, a->cam, s->cam_cell_px, st));
+            s->cam_key = a->cam; s->cam_key_set = true;
+        }
+        if (s->cam_grid.valid) {
+            a->cam_grid = s->cam_grid.d_lights; a->cam_cell_start = s->cam_grid.d_cell_start; a->cam_entries = s->cam_grid.d_entries;
+            a->cam_big = s->cam_grid.d_big; a->cam_n_big = s->cam_grid.n_big;
+        }
+    }
     a->denom = (float)(p->nb_ray * p->nb_light_sample);
     a->counters = s->d_counters;
     return RTB_OK;

@@ -119,6 +119,8 @@ struct TraceArgs {
     uint32_t pool_cap;
     // light grids (rtb_grid.cu); grid_lights == nullptr: list / walk path
     const GridLight* grid_lights; const uint32_t* grid_cell_start; const int* grid_entries; const int* grid_big; uint32_t grid_n_big;
+    // camera grid for primary rays (one GridLight, the eye); cam_grid == nullptr: BVH traversal
+    const GridLight* cam_grid; const uint32_t* cam_cell_start; const int* cam_entries; const int* cam_big; uint32_t cam_n_big;
     const GridUnion* grid_union; const uint32_t* grid_sat;
     uint32_t* masks;                     // mask_words per queued hit point: bit i = light sample i occluded
     uint32_t* queue_ctl;                 // [0] hit points queued by k_primary [1] k_shadow_plan ticket [2,3] k_shadow_queue ticket [4] walk pairs

@@ -572,11 +572,22 @@ void rtb_grid_free(RtbGrid& G) {
 
 // Builds the grids for the light points d_light_pts[0..n_lights).  On success G.valid says whether the grid path applies
 // (false: too many light points / primitives, too many un-rasterisable primitives, or the table would be too large).
+static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tris, const float4* d_light_pts, uint32_t n_lights, float y_plane,
+                                 float cell0, bool with_union, cudaStream_t st);
+
 cudaError_t rtb_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, const float4* d_light_pts, uint32_t n_lights, float cell_factor,
                            cudaStream_t st) {
     G.valid = false; G.n_lights = n_lights; G.n_big = 0; G.total_cells = 0; G.total_entries = 0; G.build_ms = 0.0f;
+    if (!G.stats_ok) return cudaSuccess;
+    // the plane sits a little below the lowest vertex so that ground-level origins project with a finite scale
+    return grid_build_ex(G, d_tris, n_tris, d_light_pts, n_lights, G.y_min - 1.0f - 1e-3f * fabsf(G.y_min), G.mean_extent * cell_factor, true, st);
+}
+
+static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tris, const float4* d_light_pts, uint32_t n_lights, float y_plane,
+                                 float cell0, bool with_union, cudaStream_t st) {
+    G.valid = false; G.n_lights = n_lights; G.n_big = 0; G.total_cells = 0; G.total_entries = 0; G.build_ms = 0.0f;
     const uint64_t work = (uint64_t)n_lights * n_tris;
-    if (!G.stats_ok || n_lights == 0 || n_lights > RTB_GRID_MAX_LIGHTS || n_tris == 0 || work > (256ull << 20)) return cudaSuccess;
+    if (!(cell0 > 0.0f) || n_lights == 0 || n_lights > RTB_GRID_MAX_LIGHTS || n_tris == 0 || work > (256ull << 20)) return cudaSuccess;
     const size_t CELL_CAP = 64u << 20, ENTRY_CAP = 512u << 20;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     GRID_CK(cudaEventCreate(&ev0)); GRID_CK(cudaEventCreate(&ev1));
@@ -589,9 +600,8 @@ cudaError_t rtb_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, co
     GRID_CK(grid_reserve(&G.d_union, &G.union_cap, (size_t)1));
     GridArgs g; memset(&g, 0, sizeof(g));
     g.tris = d_tris; g.n_tris = n_tris; g.light_pts = d_light_pts; g.n_lights = n_lights;
-    // the plane sits a little below the lowest vertex so that ground-level origins project with a finite scale
-    g.y_plane = G.y_min - 1.0f - 1e-3f * fabsf(G.y_min);
-    g.cell0 = G.mean_extent * cell_factor;
+    g.y_plane = y_plane;
+    g.cell0 = cell0;
     g.lights = G.d_lights; g.lbounds = G.d_lbounds; g.prim_flags = G.d_prim_flags; g.big_list = G.d_big; g.ctl = G.d_ctl; g.uni = G.d_union;
     g.cell_cap = (uint32_t)CELL_CAP;
     const unsigned nmax = n_lights > n_tris ? n_lights : n_tris;
@@ -627,7 +637,7 @@ cudaError_t rtb_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, co
     GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
     k_grid_raster<true><<<gw, 256, 0, st>>>(g);
     GRID_CK(cudaGetLastError());
-    {   // union occupancy + summed-area table
+    if (with_union) {   // union occupancy + summed-area table
         const int unx = (int)h_ctl[2], unz = (int)h_ctl[3];
         const size_t ns = (size_t)(unx + 1) * (size_t)(unz + 1);
         GRID_CK(grid_reserve(&G.d_sat, &G.sat_cap, ns));
@@ -646,4 +656,32 @@ cudaError_t rtb_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, co
     cudaEventDestroy(ev0); cudaEventDestroy(ev1);
     G.valid = true;
     return cudaSuccess;
+}
+
+// ---- camera grid: the same structure for primary rays ---------------------------------------------------------------------
+// Every primary ray starts at the eye: "which primitives can the ray through screen point (A, B) meet" is the same
+// query with the eye as the projection centre and the image plane as the plane.  The primitives are written once in
+// camera coordinates (x = c.u, y = -depth = c.w, z = c.v with c = vertex - eye; create_rays aims at A u + B v - D w,
+// src/main.rs:159-174), so that the eye is the origin, the plane is y = -D and the projection of a vertex is
+// (x, z) D / depth = its screen coordinates (A, B) in pixels.  One "light point" (the origin), cells of a few pixels.
+// Primitives with a vertex nearer than tau D to the eye plane or covering too many cells (the ground) go to the big list.
+__global__ void k_cam_tris(const float4* __restrict__ tris, uint32_t n, CameraBasis cam, float4* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float4 q = tris[3 * i + k];
+        const f3 c = sub3(mk3(q.x, q.y, q.z), cam.eye);
+        out[3 * i + k] = make_float4(dot3(c, cam.u), dot3(c, cam.w), dot3(c, cam.v), 0.0f);
+    }
+}
+
+cudaError_t rtb_cam_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, float4* d_cam_tris, float4* d_origin, const CameraBasis& cam,
+                               float cell_px, cudaStream_t st) {
+    G.valid = false;
+    if (n_tris == 0 || !(cam.distance > 0.0f)) return cudaSuccess;
+    k_cam_tris<<<(n_tris + 255) / 256, 256, 0, st>>>(d_tris, n_tris, cam, d_cam_tris);
+    GRID_CK(cudaMemsetAsync(d_origin, 0, sizeof(float4), st));
+    GRID_CK(cudaGetLastError());
+    return grid_build_ex(G, d_cam_tris, n_tris, d_origin, 1, -cam.distance, cell_px, false, st);
 }

@@ -49,7 +49,7 @@ def test_big_bunny_1080p_subset_exact(gpu_big_bunny, oracle_big_bunny, big_bunny
     g = gpu_big_bunny.render_pixels(pix, counters=True)
     o = oracle_big_bunny.render(S.WIDTH, S.HEIGHT, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix)
     assert_same(g, o, "big_bunny 1080p")
-    assert g["stats"]["box_tests"] > 0 and g["stats"]["tri_tests"] > 0
+    assert g["stats"]["tri_tests"] > 0          # (box tests: none on the camera-grid + light-grid path)
     assert g["stats"]["box_tests"] < o["stats"]["box_tests"] / 20     # the point of building our own tree
 
 
@@ -270,14 +270,14 @@ def test_chunked_wavefront_equals_single_pass(rtb, big_bunny_inputs, monkeypatch
     ref, st_ref = ref_sc.render(profile=True, **kw)
     pix = S.stratified_pixels(640, 360, 7, seed=2)
     ref_list = ref_sc.render_pixels(pix, **kw)
-    assert st_ref["launches"] in (3 + 5, 3 + 3)            # list / walk path or light-grid path
+    assert st_ref["launches"] in (4 + 5, 4 + 3)            # list / walk path or light-grid path (4: light table, pairs, bounds, groups)
     monkeypatch.setenv("RTB200_CHUNK_RAYS", "30000")
     sc = rtb.Scene(v, c); sc.set_samples(smp)
     got, st = sc.render(**kw)                      # chunks overlapped on two worker streams
     assert (got == ref).all()
     got2, st2 = sc.render(profile=True, **kw)      # chunks in sequence on one stream, per-kernel times
     assert (got2 == ref).all() and st2["shade_ms"] > 0 and st2["launches"] == st["launches"]
-    assert st["launches"] > 3 + 3 * 10
+    assert st["launches"] > 4 + 3 * 10
     for k in ("primary_hits", "shadow_rays", "shadow_occluded", "queued_hits", "queued_groups"):
         assert st[k] == st_ref[k], k
     got_list = sc.render_pixels(pix, **kw)
@@ -294,9 +294,10 @@ def test_list_walk_shadow_path_exact(rtb, big_bunny_inputs, oracle_big_bunny, mo
     ref, st_ref = ref_sc.render(**kw)
     assert st_ref["grid_cells"] > 0 and st_ref["grid_big"] == 1 and st_ref["queued_groups"] == 0     # grid path; big = the ground
     monkeypatch.setenv("RTB200_SHADOW", "lists")
+    monkeypatch.setenv("RTB200_PRIMARY", "bvh")           # and the BVH closest-hit traversal instead of the camera grid
     sc = rtb.Scene(v, c); sc.set_samples(smp)
-    got, st = sc.render(**kw)
-    assert st["grid_cells"] == 0 and st["queued_groups"] > 0
+    got, st = sc.render(counters=True, **kw)
+    assert st["grid_cells"] == 0 and st["queued_groups"] > 0 and st["box_tests"] > 0
     assert (got == ref).all()
     for k in ("primary_hits", "shadow_rays", "shadow_occluded"):
         assert st[k] == st_ref[k], k
@@ -331,3 +332,33 @@ def test_grid_path_geometry_around_and_above_the_light(rtb, built):
     o2 = O.OracleScene(v, c, True).render(W, H, smp, eye, look, (0.0, 0.0, -1.0), 60.0, S.LIGHT, nb_ray=1, nb_light_sample=24)
     f2, st2 = sc.render(width=W, height=H, distance=60.0, nb_ray=1, nb_light_sample=24, eye=eye, look_at=look, up=(0.0, 0.0, -1.0))
     assert (f2 == o2["rgb8"]).all() and st2["shadow_occluded"] == o2["stats"]["shadow_occluded"]
+
+
+@pytest.mark.gpu
+def test_camera_grid_eye_inside_the_scene(rtb, built, monkeypatch):
+    """Camera grid (primary rays): cameras inside a triangle soup -- primitives behind the eye, crossing the eye plane
+    or filling the screen go to the 'big' list, small ones are rasterised; full frames must equal the oracle's and the
+    BVH-traversal path's (RTB200_PRIMARY=bvh)."""
+    v, c = S.random_soup(400, seed=21)
+    smp = S.make_samples(4001, seed=8)
+    W, H = 128, 96
+    lo, hi = v.reshape(-1, 3).min(0), v.reshape(-1, 3).max(0)
+    mid = (lo + hi) / 2
+    cams = [((float(mid[0]), float(mid[1]), float(mid[2])), (float(mid[0]) + 3.0, float(mid[1]) - 1.0, float(mid[2]) - 10.0), (0.0, 1.0, 0.0), 50.0),
+            ((float(mid[0]), float(hi[1]) + 5.0, float(mid[2])), (float(mid[0]), -1000.0, float(mid[2]) + 1.0), (0.0, 0.0, -1.0), 30.0),
+            ((float(lo[0]) - 20.0, float(mid[1]), float(mid[2])), (float(hi[0]), float(mid[1]), float(mid[2])), (0.0, 1.0, 0.0), 200.0)]
+    osc = O.OracleScene(v, c, True)
+    sc = rtb.Scene(v, c); sc.set_samples(smp)
+    frames = []
+    for eye, look, up, dist in cams:
+        f, st = sc.render(width=W, height=H, distance=dist, nb_ray=2, nb_light_sample=8, eye=eye, look_at=look, up=up, counters=True)
+        o = osc.render(W, H, smp, eye, look, up, dist, S.LIGHT, nb_ray=2, nb_light_sample=8)
+        assert st["box_tests"] == 0 or st["grid_cells"] == 0       # camera grid + light grids: no BVH work (unless the light grids do not apply)
+        assert (f == o["rgb8"]).all(), (eye, int((f != o["rgb8"]).sum()))
+        assert st["primary_hits"] == o["stats"]["primary_hits"] and st["shadow_occluded"] == o["stats"]["shadow_occluded"]
+        frames.append(f)
+    monkeypatch.setenv("RTB200_PRIMARY", "bvh")
+    sb = rtb.Scene(v, c); sb.set_samples(smp)
+    for (eye, look, up, dist), f in zip(cams, frames):
+        g, _ = sb.render(width=W, height=H, distance=dist, nb_ray=2, nb_light_sample=8, eye=eye, look_at=look, up=up)
+        assert (g == f).all()
