@@ -72,6 +72,8 @@ struct rtb_scene {
     float grid_cell_factor;                      // RTB200_GRID_CELL: cell size / log-mean primitive extent
     // camera grid (rtb_grid.cu): the light-grid structure with the eye as projection centre, for primary rays
     RtbGrid cam_grid; float4* d_cam_tris; float4* d_cam_origin; CameraBasis cam_key; bool cam_key_set;
+    bool light_tables_ran;                       // the last prepare_args launched the four light-table kernels
+    bool light_key_set; uint64_t light_key_samples, light_key_need; uint32_t light_key_nb_ray, light_key_nls; cudaStream_t light_key_stream;
     int primary_mode;                            // RTB200_PRIMARY: 0 auto (camera grid when it applies), 1 bvh
     float cam_cell_px;                           // RTB200_CAM_CELL: camera-grid cell size in pixels
 };
@@ -264,7 +266,12 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         CUDA_TRY(cudaMalloc(&s->d_light_pts, (size_t)need * 3 * sizeof(float4)));      // points + pair table (k_light_pairs)
         s->light_pts_cap = (uint32_t)need;
     }
-    CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
+    // the light tables depend only on the sample table and on (nb_ray, nb_light_sample): computed once per such key.  They are
+    // produced asynchronously on `st`, so a call on another stream recomputes them (stream order is the only ordering here).
+    const bool lights_cached = s->light_key_set && s->light_key_samples == s->samples_version && s->light_key_need == need &&
+                               s->light_key_nb_ray == p->nb_ray && s->light_key_nls == p->nb_light_sample && s->light_key_stream == st;
+    s->light_tables_ran = !lights_cached;
+    if (!lights_cached) CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
     // light-sample groups (k_light_groups): at most RTB_MAX_GROUPS runs of the Hilbert-sorted samples, ~32 samples each
 #ifndef RTB_GROUP_TARGET
 #define RTB_GROUP_TARGET 32
@@ -287,8 +294,12 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         CUDA_TRY(cudaMalloc(&s->d_light_gbox, gbox_need * sizeof(float)));
         s->light_gbox_cap = gbox_need;
     }
-    CUDA_TRY(rtb_launch_light_groups(s->d_light_pts, s->d_light_box, p->nb_ray, p->nb_light_sample, s->n_samples, n_groups, group_size,
-                                     use_perm ? s->d_light_perm : nullptr, s->d_light_gbox, st));
+    if (!lights_cached) {
+        CUDA_TRY(rtb_launch_light_groups(s->d_light_pts, s->d_light_box, p->nb_ray, p->nb_light_sample, s->n_samples, n_groups, group_size,
+                                         use_perm ? s->d_light_perm : nullptr, s->d_light_gbox, st));
+        s->light_key_set = true; s->light_key_samples = s->samples_version; s->light_key_need = need; s->light_key_nb_ray = p->nb_ray;
+        s->light_key_nls = p->nb_light_sample; s->light_key_stream = st;
+    }
     // light grids: one per light point the frame addresses; cached until the table or that count changes
     if (s->shadow_mode != 1 && p->nb_ray && p->nb_light_sample &&
         !(s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need)) {
@@ -446,7 +457,7 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
         st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
         st->kernel_ms = ms;
         const bool grid = s->shadow_mode != 1 && s->grid.valid;
-        st->launches = 4 + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? (grid ? 1 : 3) : 0));   // light table, pairs, bounds, groups + per chunk
+        st->launches = (s->light_tables_ran ? 4 : 0) + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? (grid ? 1 : 3) : 0));   // light table, pairs, bounds, groups + per chunk
         st->grid_cells = grid ? s->grid.total_cells : 0; st->grid_entries = grid ? s->grid.total_entries : 0;
         st->grid_big = grid ? s->grid.n_big : 0; st->grid_build_ms = grid ? s->grid.build_ms : 0.0f;
         st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];

@@ -276,7 +276,7 @@ def test_chunked_wavefront_equals_single_pass(rtb, big_bunny_inputs, monkeypatch
     got, st = sc.render(**kw)                      # chunks overlapped on two worker streams
     assert (got == ref).all()
     got2, st2 = sc.render(profile=True, **kw)      # chunks in sequence on one stream, per-kernel times
-    assert (got2 == ref).all() and st2["shade_ms"] > 0 and st2["launches"] == st["launches"]
+    assert (got2 == ref).all() and st2["shade_ms"] > 0 and st2["launches"] == st["launches"] - 4     # the light tables are cached
     assert st["launches"] > 4 + 3 * 10
     for k in ("primary_hits", "shadow_rays", "shadow_occluded", "queued_hits", "queued_groups"):
         assert st[k] == st_ref[k], k
