@@ -334,8 +334,11 @@ __device__ __noinline__ bool lane_anyhit_walk(const TraceArgs& a, f3 o, f3 d, fl
 #ifndef RTB_GRID_R
 #define RTB_GRID_R 2
 #endif
+#ifndef RTB_GRID_BLOCKS
+#define RTB_GRID_BLOCKS 4       // resident blocks per SM the register allocation aims at
+#endif
 template <bool COUNT>
-__global__ void __launch_bounds__(256) k_shadow_grid(const TraceArgs a) {
+__global__ void __launch_bounds__(256, RTB_GRID_BLOCKS) k_shadow_grid(const TraceArgs a) {
     constexpr int R = RTB_GRID_R;
     __shared__ float4 s_o[8][32];                        // {o, self primitive}
     __shared__ float4 s_d[8][R][32];                     // {d, L}
