@@ -157,7 +157,10 @@ def main():
     scene.set_samples(samples)
     info = scene.info()
     kw = dict(nb_ray=NB_RAY, nb_light_sample=NB_LIGHT, eye=S.EYE, look_at=S.LOOK_AT, up=S.UP, distance=S.DISTANCE)
-    gather = D.BandGather(WIDTH, HEIGHT, BAND_ROWS, rank, world, dev)
+    # N > 1: every rank's shading kernel stores its pixels straight into rank 0's frame over NVLink (CUDA IPC mapping,
+    # ray_tracer_rust_b200.distributed.PeerFrame); RTB200_GATHER=nccl selects the send-buffer + NCCL gather + placement form
+    use_peer = world > 1 and os.environ.get("RTB200_GATHER", "peer") != "nccl"
+    gather = (D.PeerFrame if use_peer else D.BandGather)(WIDTH, HEIGHT, BAND_ROWS, rank, world, dev)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
     stream = torch.cuda.current_stream(dev)
 
@@ -264,7 +267,7 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "primitives": info["n_tris"], "bvh_nodes": info["n_nodes"], "band_rows": BAND_ROWS,
-                       "parallelism": "row bands b %% N over %d GPU(s), scene replicated, NCCL gather to rank 0" % world,
+                       "parallelism": ("row bands b %% N over %d GPU(s), scene replicated, " % world) + ("k_shade stores into rank 0's frame over NVLink peer memory (one kernel renders and gathers)" if use_peer else "NCCL gather to rank 0"),
                        "l2": "flushed between timed frames (256 MiB write)", "sample_table": "SplitMix64 seed 0x5EED0001, 2e6 pairs"},
             "mrays_per_s_primary_only": st["primary_rays"] / (ms_per_step * 1e-3) / 1e6,
             "rays_per_frame": {"primary": st["primary_rays"], "primary_hits": st["primary_hits"], "shadow": st["shadow_rays"],
@@ -274,7 +277,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,
                     "h2d_bytes_per_step": int(samples.nbytes + 64), "d2h_bytes_per_step": int(rows * WIDTH * 3),
                     "path": "rtb_scene_set_samples + rtb_render with pinned host buffers"},
-            "gpu_launches": args.steps * (s1["launches"] * world + (1 if world > 1 else 0)),
+            "gpu_launches": args.steps * (s1["launches"] * world + (1 if (world > 1 and not use_peer) else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
                          "traffic": None, "kernel": "wavefront chain k_primary -> k_shadow_grid -> k_shade per chunk of 16 Mi rays (per_kernel_ms: chunks in sequence, RTB_FLAG_PROFILE)",
                          "kernel_ms": kernel_ms, "per_kernel_ms": per_kernel, "shadow_queue": queue, "algorithmic_flops_per_launch": flops / world,
@@ -291,6 +294,8 @@ def main():
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()
+        if hasattr(gather, "close"):
+            gather.close()
         dist.destroy_process_group()
 
 

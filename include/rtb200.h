@@ -67,6 +67,10 @@ typedef struct {
 #define RTB_FLAG_COUNTERS 1u      /* also count AABB / triangle tests (slower instrumented kernel) */
 #define RTB_FLAG_PROFILE 2u       /* per-kernel times in rtb_stats: the chunks of the frame run one after the other on one stream
                                      instead of overlapping on two (a little slower) */
+#define RTB_FLAG_FRAME_ROWS 4u    /* rtb_render_device only: d_rgb8 is the FULL frame (height * width * 3 bytes) and every owned row is
+                                     written at its own position in it, not compactly.  With d_rgb8 = rank 0's frame mapped into this
+                                     process (rtb_peer_open) the shading kernel stores its pixels straight into the gathered frame over
+                                     NVLink: render and gather are one kernel, no staging buffer, no placement pass. */
 
 typedef struct {
     uint64_t primary_rays, primary_hits, shadow_rays, shadow_occluded;
@@ -149,6 +153,14 @@ uint32_t rtb_owned_rows(uint32_t height, uint32_t band_rows, uint32_t rank, uint
  * Replaces the put_pixel placement of src/main.rs:291-295. */
 int rtb_deinterleave_bands(int32_t device, const void* d_staged, uint64_t stride_bytes, void* d_frame,
                            uint32_t width, uint32_t height, uint32_t band_rows, uint32_t world, void* cuda_stream);
+
+/* Peer frame: the put_pixel placement of src/main.rs:291-295 across GPUs without a collective.  Rank 0 allocates the frame
+ * and exports a 64-byte CUDA IPC handle (rtb_peer_alloc); every other rank maps it (rtb_peer_open; peer access over
+ * NVLink is enabled by the mapping) and renders with RTB_FLAG_FRAME_ROWS into the mapped pointer.  The caller orders
+ * "all ranks done" -> "rank 0 reads" itself (one barrier per frame).  rtb_peer_close unmaps (owner = 0) or frees (owner = 1). */
+int rtb_peer_alloc(int32_t device, uint64_t bytes, void** d_ptr_out, uint8_t handle_out[64]);
+int rtb_peer_open(int32_t device, const uint8_t handle[64], void** d_ptr_out);
+int rtb_peer_close(int32_t device, void* d_ptr, int32_t owner);
 
 /* --- host-side entry points kept from main.rs --- */
 

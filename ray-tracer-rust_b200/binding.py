@@ -15,6 +15,7 @@ LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(_HERE, "librtb200.so")  
 
 RTB_FLAG_COUNTERS = 1
 RTB_FLAG_PROFILE = 2
+RTB_FLAG_FRAME_ROWS = 4
 
 
 class RtbError(RuntimeError):
@@ -49,7 +50,7 @@ class SceneInfo(C.Structure):
 
 
 EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_render",
-           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_import_obj",
+           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
 
 _lib = None
@@ -78,6 +79,9 @@ def lib():
         L.rtb_selftest_division.argtypes = [vp, C.c_uint64, C.c_uint64, vp]
         L.rtb_owned_rows.argtypes = [C.c_uint32] * 4; L.rtb_owned_rows.restype = C.c_uint32
         L.rtb_deinterleave_bands.argtypes = [C.c_int32, vp, C.c_uint64, vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, vp]
+        L.rtb_peer_alloc.argtypes = [C.c_int32, C.c_uint64, C.POINTER(vp), C.c_char_p]
+        L.rtb_peer_open.argtypes = [C.c_int32, C.c_char_p, C.POINTER(vp)]
+        L.rtb_peer_close.argtypes = [C.c_int32, vp, C.c_int32]
         L.rtb_import_obj.argtypes = [C.c_char_p, vp, vp]
         L.rtb_free.argtypes = [vp]; L.rtb_free.restype = None
         L.rtb_fill_samples.argtypes = [C.c_uint64, C.c_uint32, vp]; L.rtb_fill_samples.restype = None
@@ -196,13 +200,13 @@ class Scene:
     @staticmethod
     def params(width=1920, height=1080, nb_ray=1, nb_light_sample=100, eye=DEFAULT_CAMERA["eye"],
                look_at=DEFAULT_CAMERA["look_at"], up=DEFAULT_CAMERA["up"], distance=DEFAULT_CAMERA["distance"],
-               band_rows=8, rank=0, world=1, counters=False, profile=False):
+               band_rows=8, rank=0, world=1, counters=False, profile=False, frame_rows=False):
         p = RenderParams()
         p.width, p.height, p.nb_ray, p.nb_light_sample = width, height, nb_ray, nb_light_sample
         p.eye[:] = [float(x) for x in eye]; p.look_at[:] = [float(x) for x in look_at]; p.up[:] = [float(x) for x in up]
         p.distance = float(distance)
         p.band_rows, p.rank, p.world = band_rows, rank, world
-        p.flags = (RTB_FLAG_COUNTERS if counters else 0) | (RTB_FLAG_PROFILE if profile else 0)
+        p.flags = (RTB_FLAG_COUNTERS if counters else 0) | (RTB_FLAG_PROFILE if profile else 0) | (RTB_FLAG_FRAME_ROWS if frame_rows else 0)
         return p
 
     def render(self, out=None, **kw):
@@ -267,3 +271,22 @@ class Scene:
 def deinterleave_bands(device, d_staged, stride_bytes, d_frame, width, height, band_rows, world, stream=0):
     _check(lib().rtb_deinterleave_bands(device, C.c_void_p(d_staged), stride_bytes, C.c_void_p(d_frame), width, height,
                                         band_rows, world, C.c_void_p(stream)))
+
+
+def peer_alloc(device, nbytes):
+    """Rank 0: device buffer + its 64-byte CUDA IPC handle (rtb_peer_alloc)."""
+    ptr = C.c_void_p()
+    handle = C.create_string_buffer(64)
+    _check(lib().rtb_peer_alloc(device, nbytes, C.byref(ptr), handle))
+    return ptr.value, handle.raw
+
+
+def peer_open(device, handle):
+    """Other ranks: map rank 0's buffer into this process (peer access over NVLink)."""
+    ptr = C.c_void_p()
+    _check(lib().rtb_peer_open(device, bytes(handle), C.byref(ptr)))
+    return ptr.value
+
+
+def peer_close(device, ptr, owner):
+    _check(lib().rtb_peer_close(device, C.c_void_p(ptr), 1 if owner else 0))

@@ -476,7 +476,40 @@ int rtb_render_device(rtb_scene* s, const rtb_render_params* p, void* d_rgb8, vo
     if (rc != RTB_OK) return rc;
     if (!d_rgb8) return fail(RTB_ERR_ARG, "rtb_render_device: null output");
     a.rgb8 = (uint8_t*)d_rgb8;
+    a.frame_rows = (p->flags & RTB_FLAG_FRAME_ROWS) ? 1u : 0u;
     return run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, st, false);
+}
+
+int rtb_peer_alloc(int32_t device, uint64_t bytes, void** d_ptr_out, uint8_t handle_out[64]) {
+    if (!d_ptr_out || !handle_out || bytes == 0) return fail(RTB_ERR_ARG, "rtb_peer_alloc: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    CUDA_TRY(cudaSetDevice(device));
+    void* p = nullptr;
+    CUDA_TRY(cudaMalloc(&p, bytes));
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); return fail(RTB_ERR_CUDA, "cudaIpcGetMemHandle: %s", cudaGetErrorString(e)); }
+    memcpy(handle_out, &h, 64);
+    *d_ptr_out = p;
+    return RTB_OK;
+}
+
+int rtb_peer_open(int32_t device, const uint8_t handle[64], void** d_ptr_out) {
+    if (!d_ptr_out || !handle) return fail(RTB_ERR_ARG, "rtb_peer_open: bad argument");
+    CUDA_TRY(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    void* p = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *d_ptr_out = p;
+    return RTB_OK;
+}
+
+int rtb_peer_close(int32_t device, void* d_ptr, int32_t owner) {
+    if (!d_ptr) return RTB_OK;
+    CUDA_TRY(cudaSetDevice(device));
+    if (owner) CUDA_TRY(cudaFree(d_ptr)); else CUDA_TRY(cudaIpcCloseMemHandle(d_ptr));
+    return RTB_OK;
 }
 
 int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stats* stats) {

@@ -99,6 +99,7 @@ struct TraceArgs {
     const float4* __restrict__ nodes;    // 4 float4 per inner node (layout in rtb_bvh.cu)
     const float2* __restrict__ samples;  // n_samples (u,v) pairs
     const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table
+    uint32_t frame_rows;                    // 1: rgb8 is the full frame, owned rows go to their own position (RTB_FLAG_FRAME_ROWS)
     const float4* __restrict__ light_pairs; // pair table of the same points (k_light_pairs), 2 float4 per point
     const float* __restrict__ light_box; // 6 floats: component-wise min / max of light_pts[0..n_light_pts)
     const uint16_t* __restrict__ light_perm; // [nb_ray][nb_light_sample] sample at sorted position j (k_light_groups), nullptr = identity

@@ -60,11 +60,64 @@ class BandGather:
         return self.frame
 
 
+class _DevicePtr:
+    """A raw device allocation as an object torch.as_tensor can wrap (__cuda_array_interface__)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerFrame:
+    """Render + gather as ONE kernel: rank 0 owns the frame, every other rank maps it through CUDA IPC (NVLink peer
+    access) and its shading kernel stores each pixel straight into rank 0's frame at the pixel's own position
+    (RTB_FLAG_FRAME_ROWS).  No send buffers, no collective moving data, no placement pass; the only cross-rank step per
+    frame is a one-element all_reduce that orders "every rank's kernel has finished" before rank 0 reads the frame.
+    Same interface as BandGather (send / gather() / frame)."""
+
+    def __init__(self, width, height, band_rows, rank, world, device, group=None):
+        self.width, self.height, self.band_rows, self.rank, self.world = width, height, band_rows, rank, world
+        self.device = torch.device(device)
+        self.group = group
+        self.nbytes = height * width * 3
+        self.index = self.device.index or 0
+        handle = torch.zeros(64, dtype=torch.uint8, device=self.device)
+        self.owner = rank == 0
+        if self.owner:
+            self.ptr, h = binding.peer_alloc(self.index, self.nbytes)
+            handle.copy_(torch.frombuffer(bytearray(h), dtype=torch.uint8))
+        if world > 1:
+            dist.broadcast(handle, src=0, group=group)
+        if not self.owner:
+            self.ptr = binding.peer_open(self.index, bytes(handle.cpu().numpy().tobytes()))
+        self.frame = torch.as_tensor(_DevicePtr(self.ptr, self.nbytes), device=self.device) if self.owner else None
+        self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.frame_rows = True
+
+    def gather(self):
+        """Stream-ordered: after it, rank 0's self.frame holds the row-major RGB8 frame of every rank's rows."""
+        if self.world > 1:
+            dist.all_reduce(self.flag, group=self.group)
+        return self.frame
+
+    def close(self):
+        if self.ptr:
+            torch.cuda.synchronize(self.device)
+            if self.world > 1:
+                dist.barrier(group=self.group)           # nobody unmaps / frees while a peer may still write
+            self.frame = None
+            binding.peer_close(self.index, self.ptr, self.owner)
+            self.ptr = 0
+
+
 def render_distributed(scene, gather, **params):
     """One frame on this rank's bands + the gather.  Asynchronous on the current torch stream of the scene's device."""
     stream = torch.cuda.current_stream(gather.device).cuda_stream
-    scene.render_device(gather.send.data_ptr(), stream, width=gather.width, height=gather.height,
-                        band_rows=gather.band_rows, rank=gather.rank, world=gather.world, **params)
+    if getattr(gather, "frame_rows", False):             # PeerFrame: pixels go straight into rank 0's frame
+        scene.render_device(gather.ptr, stream, width=gather.width, height=gather.height, band_rows=gather.band_rows,
+                            rank=gather.rank, world=gather.world, frame_rows=True, **params)
+    else:
+        scene.render_device(gather.send.data_ptr(), stream, width=gather.width, height=gather.height,
+                            band_rows=gather.band_rows, rank=gather.rank, world=gather.world, **params)
     return gather.gather()
 
 

@@ -7,6 +7,7 @@ use std::os::raw::{c_char, c_void};
 pub const RTB_OK: i32 = 0;
 pub const RTB_FLAG_COUNTERS: u32 = 1;
 pub const RTB_FLAG_PROFILE: u32 = 2;
+pub const RTB_FLAG_FRAME_ROWS: u32 = 4;
 
 #[repr(C)]
 pub struct RtbScene { _private: [u8; 0] }
@@ -64,6 +65,9 @@ extern "C" {
     pub fn rtb_owned_rows(height: u32, band_rows: u32, rank: u32, world: u32) -> u32;
     pub fn rtb_deinterleave_bands(device: i32, d_staged: *const c_void, stride_bytes: u64, d_frame: *mut c_void,
                                   width: u32, height: u32, band_rows: u32, world: u32, cuda_stream: *mut c_void) -> i32;
+    pub fn rtb_peer_alloc(device: i32, bytes: u64, d_ptr_out: *mut *mut c_void, handle_out: *mut u8) -> i32;
+    pub fn rtb_peer_open(device: i32, handle: *const u8, d_ptr_out: *mut *mut c_void) -> i32;
+    pub fn rtb_peer_close(device: i32, d_ptr: *mut c_void, owner: i32) -> i32;
     pub fn rtb_import_obj(path: *const c_char, verts_out: *mut *mut f32, n_out: *mut u32) -> i32;
     pub fn rtb_free(p: *mut c_void);
     pub fn rtb_fill_samples(seed: u64, n_pairs: u32, out: *mut f32);

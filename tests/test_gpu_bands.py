@@ -62,3 +62,49 @@ def test_render_device_into_torch_buffer(scene):
     torch.cuda.synchronize()
     want, _ = scene.render(width=w, height=h, distance=96.0, nb_light_sample=8)
     assert (frame.cpu().numpy().reshape(h, w, 3) == want).all()
+
+
+def _peer_worker(rank, world, port, w, h, band, q):
+    import os, sys
+    ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import torch
+    import torch.distributed as dist
+    import rtb200
+    import scenes as S2
+    D = importlib.import_module("ray_tracer_rust_b200.distributed")
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)      # both ranks share cuda:0 here, which NCCL refuses
+    try:
+        v, c = S2.big_bunny()
+        sc = rtb200.Scene(v, c); sc.set_samples(S2.make_samples())
+        kw = dict(distance=288.0 * w / 1920, nb_ray=2, nb_light_sample=8)
+        pf = D.PeerFrame(w, h, band, rank, world, "cuda:0")
+        if rank == 0:
+            pf.frame.zero_()
+        torch.cuda.synchronize(); dist.barrier()
+        for _ in range(2):                                            # twice: the mapping is reused frame after frame
+            frame = D.render_distributed(sc, pf, **kw)
+        torch.cuda.synchronize(); dist.barrier()
+        if rank == 0:
+            full, _ = sc.render(width=w, height=h, **kw)
+            q.put(bool((frame.cpu().numpy().reshape(h, w, 3) == full).all()))
+        pf.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_peer_frame_two_processes_one_kernel_gather(built):
+    """Render + gather as one kernel: two processes (both on cuda:0), rank 1 maps rank 0's frame through CUDA IPC and its
+    shading kernel writes its bands straight into it; the result must equal the single-process frame."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    w, h, band, world = 320, 180, 8, 2
+    procs = [ctx.Process(target=_peer_worker, args=(r, world, 29631, w, h, band, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    assert q.get(timeout=5) is True
