@@ -27,6 +27,7 @@ cudaError_t rtb_upload_gamma_table(const float*);
 cudaError_t rtb_launch_color_to_u8(const float*, uint64_t, uint8_t*, cudaStream_t);
 cudaError_t rtb_launch_get_ranks(const float4*, uint32_t, int*, cudaStream_t);
 cudaError_t rtb_launch_div_selftest(uint64_t, uint64_t, unsigned long long*, cudaStream_t);
+cudaError_t rtb_launch_cdiv_check(float, float, float, uint32_t*, cudaStream_t);
 
 static thread_local char g_err[512] = "";
 
@@ -76,6 +77,9 @@ struct rtb_scene {
     bool light_key_set; uint64_t light_key_samples, light_key_need; uint32_t light_key_nb_ray, light_key_nls; cudaStream_t light_key_stream;
     int primary_mode;                            // RTB200_PRIMARY: 0 auto (camera grid when it applies), 1 bvh
     float cam_cell_px;                           // RTB200_CAM_CELL: camera-grid cell size in pixels
+    // two-operation division by the frame's denom (k_shade): checked exhaustively on the device once per (denom, stream)
+    uint32_t* d_cdiv_bad; float cdiv_denom; bool cdiv_key_set; cudaStream_t cdiv_stream;
+    bool cdiv_off;                               // RTB200_CDIV=0: always the three-operation shared-reciprocal division
 };
 
 // ---- Color::to_rgba threshold table (color.rs:10-33) ---------------------------------------
@@ -137,7 +141,7 @@ void rtb_scene_destroy(rtb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm); cudaFree(s->d_light_gbox);
-    cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame);
+    cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame); cudaFree(s->d_cdiv_bad);
     for (int k = 0; k < 2; ++k) {
         rtb_scene::WaveBufs& b = s->wb[k];
         cudaFree(b.d_records); cudaFree(b.d_items); cudaFree(b.d_masks); cudaFree(b.d_queue_ctl);
@@ -185,6 +189,7 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     if (const char* env = getenv("RTB200_CHUNK_RAYS")) { const long long v = atoll(env); if (v > 0) s->chunk_rays = (uint64_t)v; }
     s->shadow_mode = 0; s->grid_cell_factor = 0.25f;
     if (const char* env = getenv("RTB200_SHADOW")) s->shadow_mode = !strcmp(env, "lists") ? 1 : (!strcmp(env, "grid") ? 2 : 0);
+    if (const char* env = getenv("RTB200_CDIV")) s->cdiv_off = atoi(env) == 0;
     if (const char* env = getenv("RTB200_TRACE_CHUNKS")) s->trace_chunks = atoi(env) != 0;
     s->cam_cell_px = 2.0f;
     if (const char* env = getenv("RTB200_CAM_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->cam_cell_px = v; }
@@ -335,6 +340,16 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         }
     }
     a->denom = (float)(p->nb_ray * p->nb_light_sample);
+    if (a->denom > 0.0f && !s->cdiv_off) {
+        a->cdiv_hi = 1.0f / a->denom;
+        a->cdiv_lo = (float)(1.0 / (double)a->denom - (double)a->cdiv_hi);
+        if (!s->d_cdiv_bad) CUDA_TRY(cudaMalloc(&s->d_cdiv_bad, sizeof(uint32_t)));
+        if (!(s->cdiv_key_set && s->cdiv_denom == a->denom && s->cdiv_stream == st)) {    // stream order is the only ordering here
+            CUDA_TRY(rtb_launch_cdiv_check(a->denom, a->cdiv_hi, a->cdiv_lo, s->d_cdiv_bad, st));
+            s->cdiv_denom = a->denom; s->cdiv_stream = st; s->cdiv_key_set = true;
+        }
+        a->cdiv_bad = s->d_cdiv_bad;
+    }
     a->counters = s->d_counters;
     return RTB_OK;
 }

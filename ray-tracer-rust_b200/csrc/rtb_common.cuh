@@ -111,6 +111,8 @@ struct TraceArgs {
     uint32_t band_rows, rank, world, owned_rows;
     CameraBasis cam;
     float denom;                         // (NB_RAY * NB_LIGHT_SAMPLE) as f32 (src/main.rs:211)
+    float cdiv_hi, cdiv_lo;              // rn(1 / denom) and rn(1 / denom - cdiv_hi): the two-operation division by denom (k_shade)
+    const uint32_t* cdiv_bad;            // significands for which that form differs from `/` (k_cdiv_check); use it only if 0
     // wavefront buffers (rtb_trace.cu): hit records [nb_ray][n_pix_padded], shadow queue, occlusion masks
     uint2* records;                      // {t bits, prim | flags} per (ray r, padded pixel)
     float4* items;                       // RTB_ITEM_F4 float4 per queued hit point

@@ -362,3 +362,27 @@ def test_camera_grid_eye_inside_the_scene(rtb, built, monkeypatch):
     for (eye, look, up, dist), f in zip(cams, frames):
         g, _ = sb.render(width=W, height=H, distance=dist, nb_ray=2, nb_light_sample=8, eye=eye, look_at=look, up=up)
         assert (g == f).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nb_ray,nls", [(2, 40), (3, 7), (1, 100), (16, 100)])
+def test_two_operation_constant_division_equals_shared_reciprocal(rtb, big_bunny_inputs, oracle_big_bunny, monkeypatch, nb_ray, nls):
+    """k_shade divides by denom = NB_RAY * NB_LIGHT_SAMPLE (src/main.rs:211) with rn(x * Ch + rn(x * Cl)) once k_cdiv_check has
+    compared that form with `/` for every f32 significand; RTB200_CDIV=0 forces the three-operation shared-reciprocal
+    division.  Same bytes both ways, and both equal the oracle on ground pixels (the loop that uses it)."""
+    v, c, smp = big_bunny_inputs
+    kw = dict(width=480, height=270, distance=72.0, nb_ray=nb_ray, nb_light_sample=nls)
+    sc = rtb.Scene(v, c); sc.set_samples(smp)
+    got, _ = sc.render(**kw)
+    monkeypatch.setenv("RTB200_CDIV", "0")
+    sc0 = rtb.Scene(v, c); sc0.set_samples(smp)
+    ref, _ = sc0.render(**kw)
+    assert (got == ref).all()
+    pix = S.stratified_pixels(480, 270, 5, seed=11)
+    pix = pix[pix[:, 1] > 150]                       # ground rows
+    g = sc.render_pixels(pix, **kw)
+    g0 = sc0.render_pixels(pix, **kw)
+    assert (g["rgb_lin"].view(np.uint32) == g0["rgb_lin"].view(np.uint32)).all()
+    if nb_ray * nls <= 200:
+        o = oracle_big_bunny.render(480, 270, smp, S.EYE, S.LOOK_AT, S.UP, 72.0, S.LIGHT, nb_ray=nb_ray, nb_light_sample=nls, pixels=pix)
+        assert (g["rgb_lin"].view(np.uint32) == o["rgb_lin"].view(np.uint32)).all()
