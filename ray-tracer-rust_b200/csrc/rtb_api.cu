@@ -58,6 +58,7 @@ struct rtb_scene {
         uint2* d_records; float4* d_items; uint32_t* d_masks; uint32_t* d_queue_ctl;
         uint4* d_subitems; uint4* d_sublists; int* d_cand_pool;
         size_t rays_cap, mask_cap, sub_cap, pool_cap;
+        uint32_t* d_tile_slot; uint4* d_term_tiles; float* d_terms; size_t tile_slot_cap, term_slots, term_floats;   // term wavefront
     } wb[2];
     cudaStream_t wstream[2];
     cudaEvent_t ev_fork, ev_join[2];
@@ -79,6 +80,10 @@ struct rtb_scene {
     float cam_cell_px;                           // RTB200_CAM_CELL: camera-grid cell size in pixels
     // two-operation division by the frame's denom (k_shade): checked exhaustively on the device once per (denom, stream)
     uint32_t* d_cdiv_bad; float cdiv_denom; bool cdiv_key_set; cudaStream_t cdiv_stream;
+    bool all_grey;                               // every primitive colour has r == g == b: one term channel instead of three
+    int term_mode;                               // RTB200_TERMS: 0 auto (single-chunk renders), 1 always, -1 never
+    bool terms_ran;                              // the last render launched k_shade_terms
+    uint64_t term_bytes;                         // RTB200_TERM_MB: memory per buffer set for the term wavefront (default 1 GiB, 0 = off)
     bool cdiv_off;                               // RTB200_CDIV=0: always the three-operation shared-reciprocal division
 };
 
@@ -146,6 +151,7 @@ void rtb_scene_destroy(rtb_scene* s) {
         rtb_scene::WaveBufs& b = s->wb[k];
         cudaFree(b.d_records); cudaFree(b.d_items); cudaFree(b.d_masks); cudaFree(b.d_queue_ctl);
         cudaFree(b.d_subitems); cudaFree(b.d_sublists); cudaFree(b.d_cand_pool);
+        cudaFree(b.d_tile_slot); cudaFree(b.d_term_tiles); cudaFree(b.d_terms);
         if (s->wstream[k]) cudaStreamDestroy(s->wstream[k]);
         if (s->ev_join[k]) cudaEventDestroy(s->ev_join[k]);
     }
@@ -190,6 +196,12 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     s->shadow_mode = 0; s->grid_cell_factor = 0.25f;
     if (const char* env = getenv("RTB200_SHADOW")) s->shadow_mode = !strcmp(env, "lists") ? 1 : (!strcmp(env, "grid") ? 2 : 0);
     if (const char* env = getenv("RTB200_CDIV")) s->cdiv_off = atoi(env) == 0;
+    if (const char* env = getenv("RTB200_TERMS")) s->term_mode = !strcmp(env, "1") ? 1 : (!strcmp(env, "0") ? -1 : 0);
+    s->term_bytes = 1ull << 30;
+    if (const char* env = getenv("RTB200_TERM_MB")) { const long long v = atoll(env); if (v >= 0) s->term_bytes = (uint64_t)v << 20; }
+    s->all_grey = true;
+    for (uint32_t i = 0; i < desc->n_tris && s->all_grey; ++i)
+        s->all_grey = desc->colors[3 * i] == desc->colors[3 * i + 1] && desc->colors[3 * i + 1] == desc->colors[3 * i + 2];
     if (const char* env = getenv("RTB200_TRACE_CHUNKS")) s->trace_chunks = atoi(env) != 0;
     s->cam_cell_px = 2.0f;
     if (const char* env = getenv("RTB200_CAM_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->cam_cell_px = v; }
@@ -358,7 +370,25 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
 
 // Grows (never shrinks) the wavefront buffers of the scene to hold one chunk of `rays` rays: worst case every ray hits,
 // is queued and keeps all its light-sample groups.
-static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_groups, uint32_t mask_words, bool lists) {
+static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_groups, uint32_t mask_words, bool lists,
+                             uint64_t term_slots, uint64_t term_slot_floats) {
+    if (term_slots) {                            // term wavefront: slot table per (ray, 32-pixel tile), slot descriptors, term rows
+        if (rays / 32 > b.tile_slot_cap) {
+            cudaFree(b.d_tile_slot); b.d_tile_slot = nullptr; b.tile_slot_cap = 0;
+            CUDA_TRY(cudaMalloc(&b.d_tile_slot, rays / 32 * sizeof(uint32_t)));
+            b.tile_slot_cap = rays / 32;
+        }
+        if (term_slots > b.term_slots) {
+            cudaFree(b.d_term_tiles); b.d_term_tiles = nullptr; b.term_slots = 0;
+            CUDA_TRY(cudaMalloc(&b.d_term_tiles, term_slots * sizeof(uint4)));
+            b.term_slots = term_slots;
+        }
+        if (term_slots * term_slot_floats > b.term_floats) {
+            cudaFree(b.d_terms); b.d_terms = nullptr; b.term_floats = 0;
+            CUDA_TRY(cudaMalloc(&b.d_terms, term_slots * term_slot_floats * sizeof(float)));
+            b.term_floats = term_slots * term_slot_floats;
+        }
+    }
     if (rays > b.rays_cap) {
         cudaFree(b.d_records); cudaFree(b.d_items); b.d_records = nullptr; b.d_items = nullptr; b.rays_cap = 0;
         CUDA_TRY(cudaMalloc(&b.d_records, rays * sizeof(uint2)));
@@ -395,7 +425,7 @@ static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_g
 // in the worst case) whatever the resolution and rays per pixel.  A chunk is a whole number of tile rows (or of 256
 // listed pixels).  timed: record the per-kernel events of the first RTB_MAX_TIMED_CHUNKS chunks.
 static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st, bool timed) {
-    s->timed_chunks = 0; s->n_chunks = 0;
+    s->timed_chunks = 0; s->n_chunks = 0; s->terms_ran = false;
     uint64_t unit, units_total;                       // pixels per granule, granules
     if (a.pixel_list) {
         unit = 256; units_total = (a.n_pix + 255) / 256; a.tiles_x = 0;
@@ -416,8 +446,21 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
     // timed (per-kernel events) or a single chunk: everything on the caller's stream with buffer set 0.  Otherwise chunk c
     // runs on worker stream c & 1 with buffer set c & 1; the workers start after the caller's stream and it waits for them.
     const bool overlap = !timed && n_chunks > 1;
+    // term wavefront (k_shade_terms): as many (tile, ray) slots as fit the budget, at most one per warp of k_primary
+    a.term_channels = s->all_grey ? 1u : 3u;
+    a.term_stride = (a.nb_light_sample + 3u) & ~3u;
+    const uint64_t term_slot_floats = (uint64_t)a.term_channels * 32 * a.term_stride;
+    uint64_t term_slots = 0;
+    // Only where nothing else hides the stragglers: with several chunks the other worker stream fills the SMs a few long-running
+    // bunny warps leave idle, and the term kernel is then extra work (4K/16spp on one GPU: 17.7 ms without, 17.9 ms with); a
+    // single-chunk render -- a band share on 8 GPUs, a small frame, a pixel list -- ends on those warps (k_shade 1.15 -> 0.94 ms).
+    const bool use_terms = s->term_mode == 1 || (s->term_mode == 0 && n_chunks == 1);
+    if (a.nb_ray && a.nb_light_sample && s->term_bytes && use_terms) {
+        term_slots = s->term_bytes / (term_slot_floats * sizeof(float));
+        if (term_slots > npp_max * per_pixel / 32) term_slots = npp_max * per_pixel / 32;
+    }
     for (int k = 0; k < (overlap ? 2 : 1); ++k) {
-        const int rc = reserve_wavefront(s->wb[k], npp_max * per_pixel, a.n_groups, a.mask_words, a.grid_lights == nullptr);
+        const int rc = reserve_wavefront(s->wb[k], npp_max * per_pixel, a.n_groups, a.mask_words, a.grid_lights == nullptr, term_slots, term_slot_floats);
         if (rc != RTB_OK) return rc;
     }
     if (overlap) {
@@ -432,6 +475,8 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
         a.records = b.d_records; a.items = b.d_items; a.masks = b.d_masks; a.queue_ctl = b.d_queue_ctl; a.subitems = b.d_subitems;
         a.sublists = b.d_sublists; a.cand_pool = b.d_cand_pool; a.pool_cap = (uint32_t)b.pool_cap;
         a.queue_ticket = (unsigned long long*)(b.d_queue_ctl + 2);
+        a.tile_slot = b.d_tile_slot; a.term_tiles = b.d_term_tiles; a.terms = term_slots ? b.d_terms : nullptr; a.term_cap = (uint32_t)term_slots;
+        s->terms_ran = term_slots != 0;
         const uint64_t nu = units_total - u0 < units_per_chunk ? units_total - u0 : units_per_chunk;
         const uint64_t base = u0 * unit;
         uint64_t n = nu * unit;
@@ -472,7 +517,7 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
         st->box_tests = h[RTB_CTR_BOX]; st->tri_tests = h[RTB_CTR_TRI];
         st->kernel_ms = ms;
         const bool grid = s->shadow_mode != 1 && s->grid.valid;
-        st->launches = (s->light_tables_ran ? 4 : 0) + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? (grid ? 1 : 3) : 0));   // light table, pairs, bounds, groups + per chunk
+        st->launches = (s->light_tables_ran ? 4 : 0) + s->n_chunks * (1 + (p->nb_ray ? 1 : 0) + (p->nb_ray && p->nb_light_sample ? (grid ? 1 : 3) + (s->terms_ran ? 1 : 0) : 0));   // light table, pairs, bounds, groups + per chunk
         st->grid_cells = grid ? s->grid.total_cells : 0; st->grid_entries = grid ? s->grid.total_entries : 0;
         st->grid_big = grid ? s->grid.n_big : 0; st->grid_build_ms = grid ? s->grid.build_ms : 0.0f;
         st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];

@@ -91,6 +91,7 @@ struct RtbGrid {                   // host-side owner of the light grids of one 
 #define RTB_REC_QUEUED 0x80000000u   // record word: low 31 bits = shadow-queue slot
 #define RTB_REC_SELF 0x40000000u     // prim word: the hit primitive's own leaf is reachable (tested per ray in k_shade)
 #define RTB_PRIM_MASK 0x3fffffffu
+#define RTB_TERM_NONE 0xffffffffu
 
 // Everything a trace kernel needs, passed by value as a kernel parameter.
 struct TraceArgs {
@@ -127,8 +128,14 @@ struct TraceArgs {
     const GridUnion* grid_union; const uint32_t* grid_sat;
     uint32_t* masks;                     // mask_words per queued hit point: bit i = light sample i occluded
     uint32_t* queue_ctl;                 // [0] hit points queued by k_primary [1] k_shadow_plan ticket [2,3] k_shadow_queue ticket [4] walk pairs
-                                         // [5] of which with an entry node [6] list pairs [7] pool entries used [8,9] k_shadow_lists ticket
+                                         // [5] of which with an entry node [6] list pairs [7] pool entries used [8,9] k_shadow_lists ticket [11] term slots [12] k_shade_terms ticket
     unsigned long long* queue_ticket;    // (= queue_ctl + 2) next unclaimed ray of k_shadow_queue
+    // term wavefront (k_shade_terms): hit points on primitives whose normal is not along y have their 100 shading terms
+    // computed one warp per hit point, one lane per sample, into `terms`; k_shade then only adds them in order.
+    uint32_t* tile_slot;                 // [nb_ray][n_pix_padded / 32]: term slot of (ray r, 32-pixel tile) or RTB_TERM_NONE (k_primary)
+    uint4* term_tiles;                   // per slot: {first padded pixel of the tile, r, lanes with such a hit point, -}
+    float* terms;                        // [slot][channel < term_channels][lane][sample, row stride term_stride]; nullptr: off
+    uint32_t term_cap, term_stride, term_channels;   // slots available; floats per row (multiple of 4); 1 (all colours grey) or 3
     uint32_t n_pix_padded, tiles_x, mask_words;   // n_pix_padded: record stride of THIS chunk (multiple of 256)
     uint32_t pix_base, n_pix_chunk;      // chunk = padded pixel indices [pix_base, pix_base + n_pix_chunk)
     // outputs

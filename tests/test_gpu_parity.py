@@ -270,7 +270,7 @@ def test_chunked_wavefront_equals_single_pass(rtb, big_bunny_inputs, monkeypatch
     ref, st_ref = ref_sc.render(profile=True, **kw)
     pix = S.stratified_pixels(640, 360, 7, seed=2)
     ref_list = ref_sc.render_pixels(pix, **kw)
-    assert st_ref["launches"] in (4 + 5, 4 + 3)            # list / walk path or light-grid path (4: light table, pairs, bounds, groups)
+    assert st_ref["launches"] in (4 + 6, 4 + 4)            # list / walk path or light-grid path, + k_shade_terms (4: light table, pairs, bounds, groups)
     monkeypatch.setenv("RTB200_CHUNK_RAYS", "30000")
     sc = rtb.Scene(v, c); sc.set_samples(smp)
     got, st = sc.render(**kw)                      # chunks overlapped on two worker streams
@@ -386,3 +386,30 @@ def test_two_operation_constant_division_equals_shared_reciprocal(rtb, big_bunny
     if nb_ray * nls <= 200:
         o = oracle_big_bunny.render(480, 270, smp, S.EYE, S.LOOK_AT, S.UP, 72.0, S.LIGHT, nb_ray=nb_ray, nb_light_sample=nls, pixels=pix)
         assert (g["rgb_lin"].view(np.uint32) == o["rgb_lin"].view(np.uint32)).all()
+
+
+@pytest.mark.gpu
+def test_term_wavefront_equals_in_kernel_loops(rtb, big_bunny_inputs, monkeypatch):
+    """k_shade_terms (one warp per hit point on a non-horizontal primitive, lane = light sample; on by default for
+    single-chunk renders) against k_shade's own per-lane loops (RTB200_TERMS=0), also chunked (RTB200_TERMS=1 with tiny
+    chunks) and with a slot budget too small for the frame (the remaining tiles fall back): same bytes, same counts.
+    Grey scene (one term channel) and a coloured soup (three)."""
+    v, c, smp = big_bunny_inputs
+    sv, scol = S.random_soup(300, seed=9)
+    for verts, cols, kw in ((v, c, dict(width=640, height=360, distance=96.0, nb_ray=3, nb_light_sample=37)),
+                            (sv, scol, dict(width=320, height=180, distance=50.0, nb_ray=2, nb_light_sample=10))):
+        frames, stats = [], []
+        for env in ({"RTB200_TERMS": "0"}, {"RTB200_TERMS": "1"}, {"RTB200_TERMS": "1", "RTB200_CHUNK_RAYS": "50000"},
+                    {"RTB200_TERMS": "1", "RTB200_TERM_MB": "1"}):
+            for k in ("RTB200_TERMS", "RTB200_CHUNK_RAYS", "RTB200_TERM_MB"):
+                monkeypatch.delenv(k, raising=False)
+            for k, val in env.items():
+                monkeypatch.setenv(k, val)
+            sc = rtb.Scene(verts, cols); sc.set_samples(smp)
+            f, st = sc.render(**kw)
+            frames.append(f); stats.append(st)
+        for f, st in zip(frames[1:], stats[1:]):
+            assert (f == frames[0]).all()
+            for k in ("primary_hits", "shadow_rays", "shadow_occluded"):
+                assert st[k] == stats[0][k], k
+        assert stats[1]["launches"] == stats[0]["launches"] + 1
