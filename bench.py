@@ -26,7 +26,7 @@ import numpy as np  # noqa: E402
 WIDTH, HEIGHT, NB_RAY, NB_LIGHT = 3840, 2160, 16, 100
 WORKLOAD = "big_bunny.obj + ground, 3840x2160, NB_RAY=16, NB_LIGHT_SAMPLE=100, reference camera (distance 288)"
 METRIC = "Mrays/s (primary + shadow rays cast), big_bunny 4K 16 spp"
-BAND_ROWS = 8
+BAND_ROWS = 4                 # one tile row per band: finest interleave, per-rank times within 1.2 % at 8 GPUs (8 rows: 6 %)
 
 
 def fp32_flops(st):
@@ -119,6 +119,15 @@ def run_reference(args, rank):
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": st["threads"], "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
+
+
+def traffic_of_profile():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the chain's largest kernel from the committed ncu --set full
+    capture (profiles/r1d_traffic.json names the kernel, the launch and the report); None when absent."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r1d_traffic.json")))
+    except Exception:
+        return None
 
 
 def main():
@@ -279,7 +288,7 @@ def main():
                     "path": "rtb_scene_set_samples + rtb_render with pinned host buffers"},
             "gpu_launches": args.steps * (s1["launches"] * world + (1 if (world > 1 and not use_peer) else 0)),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-                         "traffic": None, "kernel": "wavefront chain k_primary -> k_shadow_grid -> k_shade per chunk of 16 Mi rays (per_kernel_ms: chunks in sequence, RTB_FLAG_PROFILE)",
+                         "traffic": traffic_of_profile(), "kernel": "wavefront chain k_primary -> k_shadow_grid -> k_shade per chunk of 16 Mi rays (per_kernel_ms: chunks in sequence, RTB_FLAG_PROFILE)",
                          "kernel_ms": kernel_ms, "per_kernel_ms": per_kernel, "shadow_queue": queue, "algorithmic_flops_per_launch": flops / world,
                          "peak_source": "SMs x 128 FP32 lanes x 2 x SM clock under load (%d SMs, %.0f MHz); MEASURED_PEAKS.json has no FP32 entry"
                                         % (props.multi_processor_count, sm_mhz)},
