@@ -276,7 +276,7 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "primitives": info["n_tris"], "bvh_nodes": info["n_nodes"], "band_rows": BAND_ROWS,
-                       "parallelism": ("row bands b %% N over %d GPU(s), scene replicated, " % world) + ("k_shade stores into rank 0's frame over NVLink peer memory (one kernel renders and gathers)" if use_peer else "NCCL gather to rank 0"),
+                       "parallelism": ("row bands b %% N over %d GPU(s), scene replicated, " % world) + ("k_shade stores into rank 0's frame over NVLink peer memory (one kernel renders and gathers)" if use_peer else ("no exchange" if world == 1 else "NCCL gather to rank 0")),
                        "l2": "flushed between timed frames (256 MiB write)", "sample_table": "SplitMix64 seed 0x5EED0001, 2e6 pairs"},
             "mrays_per_s_primary_only": st["primary_rays"] / (ms_per_step * 1e-3) / 1e6,
             "rays_per_frame": {"primary": st["primary_rays"], "primary_hits": st["primary_hits"], "shadow": st["shadow_rays"],

@@ -171,6 +171,16 @@ int rtb_peer_close(int32_t device, void* d_ptr, int32_t owner);
 int rtb_import_obj(const char* path, float** verts_out, uint32_t* n_out);
 void rtb_free(void* p);
 
+/* Robust OBJ + MTL import (an extension: the reference skips `mtllib` / `usemtl`, src/main.rs:130,137, and panics on anything
+ * but single-space `v x y z` / `f a b c`).  Any blank runs, CR LF, comments, `v x y z [w]`, corners `a`, `a/b`, `a//c`, `a/b/c`,
+ * negative indices, polygons (fan around the first corner).  flags & RTB_OBJ_MTL: `mtllib` (relative to the OBJ's directory)
+ * and `usemtl` are honoured; without it every triangle is white as in the reference (src/main.rs:143).
+ * Outputs (malloc'ed, rtb_free; kd_out / ks_ns_out may be NULL): verts n*9, kd n*3 (the colour to pass as
+ * rtb_scene_desc.colors), ks_ns n*4 {Ks.rgb, Ns} (models/big_bunny.mtl:4-10).  On the reference's own models the triangles
+ * equal rtb_import_obj's. */
+#define RTB_OBJ_MTL 1u
+int rtb_import_obj_ex(const char* path, uint32_t flags, float** verts_out, float** kd_out, float** ks_ns_out, uint32_t* n_out);
+
 /* Deterministic stand-in for thread_rng (src/main.rs:260-265): SplitMix64(seed) stream, value j =
  * top 24 bits * 2^-24; out holds 2*n_pairs floats. */
 void rtb_fill_samples(uint64_t seed, uint32_t n_pairs, float* out);

@@ -50,7 +50,7 @@ class SceneInfo(C.Structure):
 
 
 EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_render",
-           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj",
+           "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj", "rtb_import_obj_ex",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
 
 _lib = None
@@ -83,6 +83,7 @@ def lib():
         L.rtb_peer_open.argtypes = [C.c_int32, C.c_char_p, C.POINTER(vp)]
         L.rtb_peer_close.argtypes = [C.c_int32, vp, C.c_int32]
         L.rtb_import_obj.argtypes = [C.c_char_p, vp, vp]
+        L.rtb_import_obj_ex.argtypes = [C.c_char_p, C.c_uint32, vp, vp, vp, vp]
         L.rtb_free.argtypes = [vp]; L.rtb_free.restype = None
         L.rtb_fill_samples.argtypes = [C.c_uint64, C.c_uint32, vp]; L.rtb_fill_samples.restype = None
         L.rtb_write_png.argtypes = [C.c_char_p, vp, C.c_uint32, C.c_uint32]
@@ -118,6 +119,24 @@ def import_obj(path):
     out = np.ctypeslib.as_array(C.cast(verts, C.POINTER(C.c_float)), shape=(n.value, 9)).copy()
     lib().rtb_free(verts)
     return out
+
+
+RTB_OBJ_MTL = 1
+
+
+def import_obj_ex(path, mtl=True):
+    """Robust OBJ + MTL import (rtb_import_obj_ex; an extension, the reference skips materials, src/main.rs:130,137) ->
+    (verts (n,9), kd (n,3), ks_ns (n,4)) float32.  mtl=False: every triangle white as in the reference."""
+    verts, kd, ksns = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    n = C.c_uint32(0)
+    _check(lib().rtb_import_obj_ex(os.fsencode(path), RTB_OBJ_MTL if mtl else 0, C.byref(verts), C.byref(kd), C.byref(ksns), C.byref(n)))
+    if n.value == 0:
+        return np.zeros((0, 9), np.float32), np.zeros((0, 3), np.float32), np.zeros((0, 4), np.float32)
+    out = []
+    for ptr, w in ((verts, 9), (kd, 3), (ksns, 4)):
+        out.append(np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_float)), shape=(n.value, w)).copy())
+        lib().rtb_free(ptr)
+    return tuple(out)
 
 
 def create_ground():

@@ -20,6 +20,7 @@ int main(int argc, char** argv) {
     uint64_t seed = 0x5EED0001ull;
     int device = 0;
     std::string out = "output.png";
+    bool use_mtl = false;                        // --mtl: robust OBJ reader + Kd colours from the .mtl (extension; the reference skips materials)
     std::vector<std::string> objs;
     for (int i = 1; i < argc; ++i) {
         std::string a = argv[i];
@@ -35,22 +36,24 @@ int main(int argc, char** argv) {
         else if (a == "--seed") seed = strtoull(need("--seed"), nullptr, 0);
         else if (a == "--device") device = atoi(need("--device"));
         else if (a == "--out") out = need("--out");
+        else if (a == "--mtl") use_mtl = true;
         else objs.push_back(a);
     }
 
     printf("Building scene\n");                  // src/main.rs:322
     std::vector<float> verts, colors;
     for (const std::string& path : objs) {
-        float* v = nullptr; uint32_t n = 0;
-        int rc = rtb_import_obj(path.c_str(), &v, &n);
+        float* v = nullptr; float* kd = nullptr; uint32_t n = 0;
+        int rc = use_mtl ? rtb_import_obj_ex(path.c_str(), RTB_OBJ_MTL, &v, &kd, nullptr, &n) : rtb_import_obj(path.c_str(), &v, &n);
         if (rc != RTB_OK) {
             if (n == 0 && strncmp(rtb_last_error(), "Not a valid path", 16) == 0) { printf("%s\n", rtb_last_error()); continue; }
             fprintf(stderr, "%s\n", rtb_last_error());
             return 1;
         }
         verts.insert(verts.end(), v, v + (size_t)n * 9);
-        for (uint32_t k = 0; k < n; ++k) { colors.push_back(1.0f); colors.push_back(1.0f); colors.push_back(1.0f); }   // :143
-        rtb_free(v);
+        if (kd) colors.insert(colors.end(), kd, kd + (size_t)n * 3);
+        else for (uint32_t k = 0; k < n; ++k) { colors.push_back(1.0f); colors.push_back(1.0f); colors.push_back(1.0f); }   // :143
+        rtb_free(v); rtb_free(kd);
     }
     const float ground[9] = {-10000.0f, 0.0f, -10000.0f, 10000.0f, 0.0f, -10000.0f, 0.0f, 0.0f, 10000.0f};   // :102-111
     verts.insert(verts.end(), ground, ground + 9);

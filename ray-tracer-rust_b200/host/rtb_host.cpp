@@ -101,6 +101,151 @@ extern "C" int rtb_import_obj(const char* path, float** verts_out, uint32_t* n_o
     return RTB_OK;
 }
 
+// ---- robust OBJ + MTL import ---------------------------------------------------------------------
+// The reference's import_obj (src/main.rs:114-149) panics or mis-parses on anything but `v x y z` / `f a b c` separated by
+// single spaces, and skips `mtllib` / `usemtl` (src/main.rs:130,137: every OBJ triangle is white).  This entry point reads
+// what exporters actually write: any run of spaces / tabs, CR LF, comments, `v x y z [w]`, face corners `a`, `a/b`, `a//c`,
+// `a/b/c`, negative (relative) indices, polygons (fan-triangulated around the first corner, in corner order) and -- with
+// RTB_OBJ_MTL -- `mtllib` / `usemtl`, giving each triangle the material's Kd / Ks / Ns (models/big_bunny.mtl:4-10).  On the
+// reference's own two models it returns exactly the triangles of rtb_import_obj (tests/test_host.py).
+namespace {
+struct Material { std::string name; float kd[3] = {1.0f, 1.0f, 1.0f}, ks[3] = {0.0f, 0.0f, 0.0f}, ns = 0.0f; };
+
+bool read_file(const std::string& path, std::string* out) {
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return false;
+    char buf[1 << 16];
+    size_t got;
+    while ((got = fread(buf, 1, sizeof(buf), f)) > 0) out->append(buf, got);
+    fclose(f);
+    return true;
+}
+
+// tokens of one line: runs of non-blank characters; a '#' starts a comment
+void split_ws(const std::string& data, size_t b, size_t e, std::vector<std::string>* tok) {
+    tok->clear();
+    size_t i = b;
+    while (i < e) {
+        while (i < e && (data[i] == ' ' || data[i] == '\t' || data[i] == '\r')) ++i;
+        if (i >= e || data[i] == '#') break;
+        size_t j = i;
+        while (j < e && data[j] != ' ' && data[j] != '\t' && data[j] != '\r') ++j;
+        tok->push_back(data.substr(i, j - i));
+        i = j;
+    }
+}
+
+bool parse_mtl(const std::string& path, std::vector<Material>* mats) {
+    std::string data;
+    if (!read_file(path, &data)) return false;
+    std::vector<std::string> tok;
+    size_t pos = 0;
+    while (pos < data.size()) {
+        size_t eol = data.find('\n', pos);
+        if (eol == std::string::npos) eol = data.size();
+        split_ws(data, pos, eol, &tok);
+        pos = eol + 1;
+        if (tok.empty()) continue;
+        if (tok[0] == "newmtl") { Material m; m.name = tok.size() > 1 ? tok[1] : ""; mats->push_back(m); continue; }
+        if (mats->empty()) continue;
+        Material& m = mats->back();
+        float v[3];
+        if ((tok[0] == "Kd" || tok[0] == "Ks") && tok.size() >= 4 && parse_f32(tok[1], &v[0]) && parse_f32(tok[2], &v[1]) && parse_f32(tok[3], &v[2]))
+            memcpy(tok[0] == "Kd" ? m.kd : m.ks, v, sizeof(v));
+        else if (tok[0] == "Ns" && tok.size() >= 2 && parse_f32(tok[1], &v[0])) m.ns = v[0];
+    }
+    return true;
+}
+
+// one face corner `a`, `a/b`, `a//c`, `a/b/c`: the vertex index (1-based, or negative = relative to the vertices read so far)
+bool parse_corner(const std::string& tok, size_t nv, size_t* out) {
+    const std::string a = tok.substr(0, tok.find('/'));
+    if (a.empty()) return false;
+    char* end = nullptr;
+    errno = 0;
+    const long long v = strtoll(a.c_str(), &end, 10);
+    if (end == a.c_str() || *end != '\0' || errno) return false;
+    long long idx = v > 0 ? v - 1 : (long long)nv + v;
+    if (v == 0 || idx < 0 || (unsigned long long)idx >= nv) return false;
+    *out = (size_t)idx;
+    return true;
+}
+}  // namespace
+
+extern "C" int rtb_import_obj_ex(const char* path, uint32_t flags, float** verts_out, float** kd_out, float** ks_ns_out, uint32_t* n_out) {
+    if (!path || !verts_out || !n_out) return hfail(RTB_ERR_ARG, "rtb_import_obj_ex: null argument");
+    *verts_out = nullptr; *n_out = 0;
+    if (kd_out) *kd_out = nullptr;
+    if (ks_ns_out) *ks_ns_out = nullptr;
+    std::string data;
+    if (!read_file(path, &data)) return hfail(RTB_ERR_IO, std::string("Not a valid path: ") + path);   // message of src/main.rs:118
+    std::string dir = path;
+    const size_t slash = dir.find_last_of("/\\");
+    dir = slash == std::string::npos ? std::string() : dir.substr(0, slash + 1);
+
+    std::vector<float> vertices, tris, kd, ksns;
+    std::vector<Material> mats;
+    Material cur;                                                  // default: white, no specular (src/main.rs:143)
+    std::vector<std::string> tok;
+    std::vector<size_t> corner;
+    size_t pos = 0, line_no = 0;
+    while (pos < data.size()) {
+        size_t eol = data.find('\n', pos);
+        if (eol == std::string::npos) eol = data.size();
+        split_ws(data, pos, eol, &tok);
+        pos = eol + 1;
+        ++line_no;
+        if (tok.empty()) continue;
+        if (tok[0] == "v") {
+            float x, y, z;
+            if (tok.size() < 4 || !parse_f32(tok[1], &x) || !parse_f32(tok[2], &y) || !parse_f32(tok[3], &z))
+                return hfail(RTB_ERR_IO, std::string(path) + ": malformed vertex at line " + std::to_string(line_no));
+            vertices.push_back(x); vertices.push_back(y); vertices.push_back(z);
+        } else if (tok[0] == "f") {
+            corner.clear();
+            for (size_t k = 1; k < tok.size(); ++k) {
+                size_t idx;
+                if (!parse_corner(tok[k], vertices.size() / 3, &idx))
+                    return hfail(RTB_ERR_IO, std::string(path) + ": malformed face at line " + std::to_string(line_no));
+                corner.push_back(idx);
+            }
+            if (corner.size() < 3) return hfail(RTB_ERR_IO, std::string(path) + ": face with fewer than 3 corners at line " + std::to_string(line_no));
+            for (size_t k = 1; k + 1 < corner.size(); ++k) {       // fan around the first corner
+                const size_t tri[3] = {corner[0], corner[k], corner[k + 1]};
+                for (int c3 = 0; c3 < 3; ++c3)
+                    for (int c = 0; c < 3; ++c) tris.push_back(vertices[3 * tri[c3] + c]);
+                for (int c = 0; c < 3; ++c) kd.push_back(cur.kd[c]);
+                for (int c = 0; c < 3; ++c) ksns.push_back(cur.ks[c]);
+                ksns.push_back(cur.ns);
+            }
+        } else if ((flags & RTB_OBJ_MTL) && tok[0] == "mtllib") {
+            for (size_t k = 1; k < tok.size(); ++k)
+                if (!parse_mtl(dir + tok[k], &mats)) return hfail(RTB_ERR_IO, std::string(path) + ": cannot read material library " + dir + tok[k]);
+        } else if ((flags & RTB_OBJ_MTL) && tok[0] == "usemtl") {
+            const std::string name = tok.size() > 1 ? tok[1] : "";
+            bool found = false;
+            for (const Material& m : mats) if (m.name == name) { cur = m; found = true; }
+            if (!found) return hfail(RTB_ERR_IO, std::string(path) + ": unknown material '" + name + "' at line " + std::to_string(line_no));
+        }
+    }
+    const size_t n = tris.size() / 9;
+    if (n > 0xffffffffull) return hfail(RTB_ERR_LIMIT, "rtb_import_obj_ex: too many triangles");
+    if (n) {
+        float* v = (float*)malloc(tris.size() * sizeof(float));
+        float* k1 = kd_out ? (float*)malloc(kd.size() * sizeof(float)) : nullptr;
+        float* k2 = ks_ns_out ? (float*)malloc(ksns.size() * sizeof(float)) : nullptr;
+        if (!v || (kd_out && !k1) || (ks_ns_out && !k2)) { free(v); free(k1); free(k2); return hfail(RTB_ERR_IO, "rtb_import_obj_ex: out of memory"); }
+        memcpy(v, tris.data(), tris.size() * sizeof(float));
+        if (k1) memcpy(k1, kd.data(), kd.size() * sizeof(float));
+        if (k2) memcpy(k2, ksns.data(), ksns.size() * sizeof(float));
+        *verts_out = v;
+        if (kd_out) *kd_out = k1;
+        if (ks_ns_out) *ks_ns_out = k2;
+    }
+    *n_out = (uint32_t)n;
+    return RTB_OK;
+}
+
 extern "C" void rtb_free(void* p) { free(p); }
 
 extern "C" void rtb_fill_samples(uint64_t seed, uint32_t n_pairs, float* out) {

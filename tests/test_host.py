@@ -122,3 +122,47 @@ def test_product_never_touches_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".rs", "Makefile")):
                 txt = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "oracle" not in txt.lower().replace("no oracle", ""), os.path.join(dirpath, f)
+
+
+def test_import_obj_ex_equals_reference_rules_on_the_shipped_models(rtb):
+    """The robust reader returns exactly the reference reader's triangles on the reference's own OBJs; with materials on,
+    big_bunny.obj's `usemtl None` faces carry Kd 0.8 / Ks 0.8 / Ns 0 (models/big_bunny.mtl:4-10), bunny.obj has no
+    material statements and stays white."""
+    for name in ("big_bunny.obj", "bunny.obj"):
+        path = os.path.join(S.MODELS, name)
+        v, kd, ksns = rtb.import_obj_ex(path, mtl=False)
+        assert (v.view(np.uint32) == rtb.import_obj(path).view(np.uint32)).all()
+        assert (kd == 1.0).all() and (ksns == 0.0).all()
+    v, kd, ksns = rtb.import_obj_ex(os.path.join(S.MODELS, "big_bunny.obj"), mtl=True)
+    assert v.shape == (4968, 9) and (kd == np.float32(0.8)).all()
+    assert (ksns[:, :3] == np.float32(0.8)).all() and (ksns[:, 3] == 0.0).all()
+    v, kd, ksns = rtb.import_obj_ex(os.path.join(S.MODELS, "bunny.obj"), mtl=True)
+    assert (kd == 1.0).all()
+
+
+def test_import_obj_ex_robust_syntax(rtb, tmp_path):
+    """What the reference's reader panics on or mis-parses (src/main.rs:128-140): blank runs, tabs, CR LF, corner forms
+    a/b/c, a//c, a/b, negative indices, polygons (fan), w coordinates, comments; materials switch per usemtl."""
+    (tmp_path / "m.mtl").write_text("newmtl red\r\nKd 1 0 0\nKs 0.5 0.5 0.5\nNs 32\n\nnewmtl blue\n  Kd 0 0 1\n")
+    p = tmp_path / "a.obj"
+    p.write_text("# comment\nmtllib m.mtl\no thing\n"
+                 "v  0 0 0\nv\t1 0 0 1.0\r\nv 1  1 0\nv 0 1 0   # trailing\nvn 0 0 1\nvt 0 0\n"
+                 "usemtl red\nf 1/1/1 2/1/1 3/1/1\n"
+                 "usemtl blue\nf 1//1 2//1 3//1 4//1\n"           # quad -> (1,2,3), (1,3,4)
+                 "f -4 -3 -2\n"
+                 "s off\nf 1/1 3/1 4/1")
+    v, kd, ksns = rtb.import_obj_ex(str(p))
+    A, B, Cc, D = [0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0]
+    assert v.tolist() == [A + B + Cc, A + B + Cc, A + Cc + D, A + B + Cc, A + Cc + D]
+    assert kd.tolist() == [[1, 0, 0]] + [[0, 0, 1]] * 4
+    assert ksns.tolist() == [[0.5, 0.5, 0.5, 32.0]] + [[0, 0, 0, 0]] * 4
+    v2, kd2, _ = rtb.import_obj_ex(str(p), mtl=False)
+    assert (v2 == v).all() and (kd2 == 1.0).all()
+    for bad in ("v 0 0 0\nf 1 2 3\n", "v 0 0 0\nf 1 1\n", "v 0 0 0\nf 0 1 1\n", "v 0 0 0\nusemtl nope\nf 1 1 1\n", "mtllib missing.mtl\n",
+                "v 0 0\n", "v 0 0 0\nf -2 1 1\n"):
+        q = tmp_path / "bad.obj"
+        q.write_text(bad)
+        with pytest.raises(rtb.RtbError):
+            rtb.import_obj_ex(str(q))
+    with pytest.raises(rtb.RtbError):
+        rtb.import_obj_ex(str(tmp_path / "missing.obj"))
