@@ -424,7 +424,7 @@ static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_g
 // list, in chunks of at most s->chunk_rays rays so that the intermediate buffers stay bounded (about 170 bytes per ray
 // in the worst case) whatever the resolution and rays per pixel.  A chunk is a whole number of tile rows (or of 256
 // listed pixels).  timed: record the per-kernel events of the first RTB_MAX_TIMED_CHUNKS chunks.
-static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st, bool timed) {
+static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st, bool timed, uint8_t* h_rows = nullptr) {
     s->timed_chunks = 0; s->n_chunks = 0; s->terms_ran = false;
     uint64_t unit, units_total;                       // pixels per granule, granules
     if (a.pixel_list) {
@@ -486,6 +486,13 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
         cudaEvent_t* ev = nullptr;
         if (timed && s->timed_chunks < RTB_MAX_TIMED_CHUNKS) ev = s->evp + 4 * s->timed_chunks++;
         CUDA_TRY(rtb_launch_trace(a, count, cs, ev));
+        if (h_rows && !a.pixel_list && !a.frame_rows) {
+            // pinned host frame (rtb_render): the rows of this chunk leave right behind its k_shade, on the chunk's own stream,
+            // so the device-to-host copy of one chunk overlaps the kernels of the next
+            const uint64_t r0 = u0 * 4 < a.owned_rows ? u0 * 4 : a.owned_rows, r1 = (u0 + nu) * 4 < a.owned_rows ? (u0 + nu) * 4 : a.owned_rows;
+            const size_t off = (size_t)r0 * a.width * 3, bytes = (size_t)(r1 - r0) * a.width * 3;
+            if (bytes) CUDA_TRY(cudaMemcpyAsync(h_rows + off, a.rgb8 + off, bytes, cudaMemcpyDeviceToHost, cs));
+        }
         s->n_chunks++;
     }
     if (overlap) {
@@ -585,10 +592,14 @@ int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stat
     }
     a.rgb8 = s->d_frame;
     CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
-    rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0);
+    // a pinned destination takes per-chunk copies (an asynchronous copy to pageable memory would block the host chunk by chunk)
+    cudaPointerAttributes pa;
+    const bool pinned = cudaPointerGetAttributes(&pa, rgb8) == cudaSuccess && pa.type == cudaMemoryTypeHost && !(p->flags & RTB_FLAG_PROFILE);
+    if (!pinned) cudaGetLastError();
+    rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0, pinned ? rgb8 : nullptr);
     if (rc != RTB_OK) return rc;
     CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
-    if (bytes) CUDA_TRY(cudaMemcpyAsync(rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
+    if (bytes && !pinned) CUDA_TRY(cudaMemcpyAsync(rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
     float ms = 0.0f;
     CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));

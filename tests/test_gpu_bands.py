@@ -108,3 +108,20 @@ def test_peer_frame_two_processes_one_kernel_gather(built):
         p.join(300)
     assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
     assert q.get(timeout=5) is True
+
+
+def test_render_into_pinned_host_rows_chunk_by_chunk(built, big_bunny_inputs, monkeypatch):
+    """rtb_render with a pinned destination copies each chunk's rows behind its k_shade on the chunk's own stream; same
+    bytes as the single copy into pageable memory, for a full frame and for a band share, with many small chunks."""
+    import torch
+    import rtb200
+    v, c, smp = big_bunny_inputs
+    monkeypatch.setenv("RTB200_CHUNK_RAYS", "6000")
+    sc = rtb200.Scene(v, c); sc.set_samples(smp)
+    for kw in (dict(width=640, height=362, distance=96.0, nb_ray=2, nb_light_sample=9),
+               dict(width=333, height=187, distance=60.0, nb_ray=1, nb_light_sample=5, band_rows=4, rank=1, world=3)):
+        want, st = sc.render(**kw)
+        assert st["launches"] > 8                                    # several chunks
+        pinned = torch.zeros(want.size, dtype=torch.uint8).pin_memory()
+        got, _ = sc.render(out=pinned.numpy().reshape(want.shape), **kw)
+        assert (got == want).all()
