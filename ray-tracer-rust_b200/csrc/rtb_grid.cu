@@ -19,6 +19,8 @@
 // or that would cover too many cells (the ground) are not rasterised at all: they go to a short "big" list that every
 // ray tests.  Rays whose origin is not clearly below their light point walk the BVH instead (lane_anyhit_walk).
 #include "rtb_device.cuh"
+#include <cstdio>
+#include <cstdlib>
 #include <cub/cub.cuh>
 
 #define RTB_GRID_TAU 0.02f            // a point is projectable from P if P.y - y > TAU * (P.y - y_plane): magnification <= 50
@@ -590,7 +592,11 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
                                  float cell0, bool with_union, cudaStream_t st) {
     G.valid = false; G.n_lights = n_lights; G.n_big = 0; G.total_cells = 0; G.total_entries = 0; G.build_ms = 0.0f;
     const uint64_t work = (uint64_t)n_lights * n_tris;
-    if (!(cell0 > 0.0f) || n_lights == 0 || n_lights > RTB_GRID_MAX_LIGHTS || n_tris == 0 || work > (256ull << 20)) return cudaSuccess;
+    static const bool dbg = getenv("RTB200_GRID_DEBUG") != nullptr;
+    if (!(cell0 > 0.0f) || n_lights == 0 || n_lights > RTB_GRID_MAX_LIGHTS || n_tris == 0 || work > (256ull << 20)) {
+        if (dbg) fprintf(stderr, "rtb200 grid: not applicable (cell0 %g, lights %u, tris %u, work %llu)\n", cell0, n_lights, n_tris, (unsigned long long)work);
+        return cudaSuccess;
+    }
     const size_t CELL_CAP = 64u << 20, ENTRY_CAP = 512u << 20;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     GRID_CK(cudaEventCreate(&ev0)); GRID_CK(cudaEventCreate(&ev1));
@@ -608,16 +614,26 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     g.lights = G.d_lights; g.lbounds = G.d_lbounds; g.prim_flags = G.d_prim_flags; g.big_list = G.d_big; g.ctl = G.d_ctl; g.uni = G.d_union;
     g.cell_cap = (uint32_t)CELL_CAP;
     const unsigned nmax = n_lights > n_tris ? n_lights : n_tris;
-    k_grid_init<<<(nmax + 255) / 256, 256, 0, st>>>(G.d_lbounds, n_lights, G.d_prim_flags, n_tris, G.d_ctl);
     const unsigned gw = (unsigned)((work + 255) / 256);
-    k_grid_classify<<<gw, 256, 0, st>>>(g);
-    k_grid_biglist<<<(n_tris + 255) / 256, 256, 0, st>>>(g);
-    k_grid_layout<<<1, 1024, 0, st>>>(g);
-    GRID_CK(cudaGetLastError());
     uint32_t h_ctl[4] = {0, 0, 0, 0};
-    GRID_CK(cudaMemcpyAsync(h_ctl, G.d_ctl, sizeof(h_ctl), cudaMemcpyDeviceToHost, st));
-    GRID_CK(cudaStreamSynchronize(st));
+    // A primitive that would cover more than RTB_GRID_MAX_CELLS_PER_PRIM cells of some light's grid goes to the `big` list every
+    // ray tests.  That is meant for the ground; in a wide scene (64 bunnies over 1600 x 1400 units) the stretched projections of
+    // distant primitives cross the limit by the thousand at the cell size the primitives' own extent suggests.  Coarser cells
+    // bring them back into the grids: the classification is repeated with doubled cells while the list overflows.
+    for (int attempt = 0; ; ++attempt) {
+        k_grid_init<<<(nmax + 255) / 256, 256, 0, st>>>(G.d_lbounds, n_lights, G.d_prim_flags, n_tris, G.d_ctl);
+        k_grid_classify<<<gw, 256, 0, st>>>(g);
+        k_grid_biglist<<<(n_tris + 255) / 256, 256, 0, st>>>(g);
+        k_grid_layout<<<1, 1024, 0, st>>>(g);
+        GRID_CK(cudaGetLastError());
+        GRID_CK(cudaMemcpyAsync(h_ctl, G.d_ctl, sizeof(h_ctl), cudaMemcpyDeviceToHost, st));
+        GRID_CK(cudaStreamSynchronize(st));
+        if (h_ctl[1] <= RTB_GRID_MAX_BIG || attempt >= 5) break;
+        g.cell0 *= 2.0f;
+        if (dbg) fprintf(stderr, "rtb200 grid: %u big primitives, cells doubled to %g\n", h_ctl[1], g.cell0);
+    }
     G.total_cells = h_ctl[0]; G.n_big = h_ctl[1];
+    if (dbg) fprintf(stderr, "rtb200 grid: %u lights, %u cells, %u big primitives (max %u)\n", n_lights, G.total_cells, G.n_big, (unsigned)RTB_GRID_MAX_BIG);
     if (G.n_big > RTB_GRID_MAX_BIG || G.total_cells > CELL_CAP) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return cudaSuccess; }
     const size_t nc = (size_t)G.total_cells + 1;
     GRID_CK(grid_reserve(&G.d_cell_start, &G.cell_start_cap, nc));
@@ -634,6 +650,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     GRID_CK(cudaMemcpyAsync(&h_total, G.d_cell_start + G.total_cells, sizeof(h_total), cudaMemcpyDeviceToHost, st));
     GRID_CK(cudaStreamSynchronize(st));
     G.total_entries = h_total;
+    if (dbg) fprintf(stderr, "rtb200 grid: %u entries (cap %zu)\n", h_total, ENTRY_CAP);
     if ((size_t)h_total > ENTRY_CAP) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return cudaSuccess; }
     GRID_CK(grid_reserve(&G.d_entries, &G.entries_cap, (size_t)h_total + 1));
     g.entries = G.d_entries;

@@ -69,6 +69,8 @@ extern "C" {
     pub fn rtb_peer_open(device: i32, handle: *const u8, d_ptr_out: *mut *mut c_void) -> i32;
     pub fn rtb_peer_close(device: i32, d_ptr: *mut c_void, owner: i32) -> i32;
     pub fn rtb_import_obj(path: *const c_char, verts_out: *mut *mut f32, n_out: *mut u32) -> i32;
+    pub fn rtb_import_obj_ex(path: *const c_char, flags: u32, verts_out: *mut *mut f32, kd_out: *mut *mut f32,
+                             ks_ns_out: *mut *mut f32, n_out: *mut u32) -> i32;
     pub fn rtb_free(p: *mut c_void);
     pub fn rtb_fill_samples(seed: u64, n_pairs: u32, out: *mut f32);
     pub fn rtb_write_png(path: *const c_char, rgb8: *const u8, width: u32, height: u32) -> i32;

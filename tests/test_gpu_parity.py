@@ -353,7 +353,8 @@ def test_camera_grid_eye_inside_the_scene(rtb, built, monkeypatch):
     for eye, look, up, dist in cams:
         f, st = sc.render(width=W, height=H, distance=dist, nb_ray=2, nb_light_sample=8, eye=eye, look_at=look, up=up, counters=True)
         o = osc.render(W, H, smp, eye, look, up, dist, S.LIGHT, nb_ray=2, nb_light_sample=8)
-        assert st["box_tests"] == 0 or st["grid_cells"] == 0       # camera grid + light grids: no BVH work (unless the light grids do not apply)
+        # camera grid + light grids: no BVH work but for the rays through camera cells that list more than RTB_CAM_DENSE primitives
+        assert st["box_tests"] <= st["primary_rays"] or st["grid_cells"] == 0
         assert (f == o["rgb8"]).all(), (eye, int((f != o["rgb8"]).sum()))
         assert st["primary_hits"] == o["stats"]["primary_hits"] and st["shadow_occluded"] == o["stats"]["shadow_occluded"]
         frames.append(f)
