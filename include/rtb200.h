@@ -99,6 +99,13 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out);
 void rtb_scene_destroy(rtb_scene* scene);
 int rtb_scene_get_info(const rtb_scene* scene, rtb_scene_info* info);
 
+/* Extension (the reference reads no materials, src/main.rs:130,137, and has no specular term): ks_ns = n_tris * 4
+ * floats {Ks.rgb, Ns} (HOST, e.g. from rtb_import_obj_ex) switches the shading of a lit sample from (c * |n.l|) / denom to
+ * (c * |n.l| + Ks * max(0, r.v)^Ns) / denom with r = 2 |n.l| n_f - l (n_f: the normal on the light's side) and v the unit
+ * vector from the hit point to the eye.  NULL switches back to the reference's Lambert (the default).  Every other rule of
+ * the path is unchanged; with Ks = 0 the pixels are those of the default path bit for bit. */
+int rtb_scene_set_materials(rtb_scene* scene, const float* ks_ns);
+
 /* --- replaces the random_samples table of render() (src/main.rs:253,260-265): n_pairs (u,v)
  *     pairs in [0,1).  Must be called before any render.  The table is an explicit input
  *     because the reference draws it from an OS-seeded RNG. */

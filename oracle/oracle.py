@@ -49,6 +49,7 @@ def lib():
         L.orc_scene_create.restype = C.c_void_p
         L.orc_scene_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]
         L.orc_scene_destroy.argtypes = [C.c_void_p]
+        L.orc_scene_set_materials.argtypes = [C.c_void_p, C.c_void_p]; L.orc_scene_set_materials.restype = None
         L.orc_scene_num_nodes.argtypes = [C.c_void_p]
         L.orc_scene_dfs_rank.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_tri_normal.argtypes = [C.c_void_p, C.c_int32, C.c_void_p]
@@ -101,6 +102,15 @@ class OracleScene:
         if lib().orc_scene_dfs_rank(self._h, _ptr(r)) != 0:
             raise RuntimeError("reference tree was not built")
         return r
+
+    def set_materials(self, ks_ns):
+        """Phong extension (not in the reference): (n,4) {Ks.rgb, Ns} or None."""
+        if ks_ns is None:
+            lib().orc_scene_set_materials(self._h, None)
+        else:
+            k = _f32(ks_ns).reshape(-1, 4)
+            assert k.shape[0] == self.n
+            lib().orc_scene_set_materials(self._h, _ptr(k))
 
     def normal(self, p):
         out = np.zeros(3, dtype=np.float32)

@@ -233,6 +233,7 @@ struct Scene {
     int root;
     std::vector<int> dfs_order;    // primitive ids in left-to-right leaf order
     bool has_tree;
+    std::vector<float> ksns;       // Phong extension: {Ks.rgb, Ns} per primitive; empty = the reference's shading
 };
 
 // bvh.rs:173-226.  Agglomerative pairing on the distance between box
@@ -420,7 +421,19 @@ void render_pixel(const Scene& s, const Params& P, uint32_t px, uint32_t py, Pix
                     lit = true;
                 }
             }
-            if (lit) {
+            if (lit && !s.ksns.empty()) {
+                // Phong extension (NOT in the reference, which reads no materials: src/main.rs:130,137):
+                // + Ks * max(0, r . v)^Ns with r = 2 |n . l| n_f - l, n_f the normal on the light's side, v towards the eye
+                const float* k = &s.ksns[4 * (size_t)hit.prim];
+                V3 nf = dot(T.normal, sr.d) >= 0.0f ? T.normal : V3{-T.normal.x, -T.normal.y, -T.normal.z};
+                V3 rr = sub(scale(2.0f * lnd, nf), sr.d);
+                Ray vr = make_ray(p_hit, sub(P.cam.eye, p_hit));
+                float rv = dot(rr, vr.d);
+                float sp = rv > 0.0f ? powf(rv, k[3]) : 0.0f;
+                avg[0] = avg[0] + ((T.color.x * lnd + k[0] * sp) / denom);
+                avg[1] = avg[1] + ((T.color.y * lnd + k[1] * sp) / denom);
+                avg[2] = avg[2] + ((T.color.z * lnd + k[2] * sp) / denom);
+            } else if (lit) {
                 avg[0] = avg[0] + ((T.color.x * lnd) / denom);
                 avg[1] = avg[1] + ((T.color.y * lnd) / denom);
                 avg[2] = avg[2] + ((T.color.z * lnd) / denom);
@@ -480,6 +493,12 @@ orc_scene* orc_scene_create(const float* verts, const float* colors, int32_t n, 
 }
 
 void orc_scene_destroy(orc_scene* sc) { delete sc; }
+
+// Phong extension: n*4 floats {Ks.rgb, Ns}, or NULL for the reference's shading (see render_pixel)
+void orc_scene_set_materials(orc_scene* sc, const float* ks_ns) {
+    sc->s.ksns.clear();
+    if (ks_ns) sc->s.ksns.assign(ks_ns, ks_ns + 4 * sc->s.tris.size());
+}
 
 int32_t orc_scene_num_nodes(const orc_scene* sc) { return (int32_t)sc->s.nodes.size(); }
 

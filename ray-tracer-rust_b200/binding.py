@@ -49,7 +49,7 @@ class SceneInfo(C.Structure):
                 ("sah_cost", C.c_float), ("build_ms", C.c_float)]
 
 
-EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_render",
+EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render",
            "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj", "rtb_import_obj_ex",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
 
@@ -69,6 +69,7 @@ def lib():
         L.rtb_scene_destroy.argtypes = [vp]; L.rtb_scene_destroy.restype = None
         L.rtb_scene_get_info.argtypes = [vp, vp]
         L.rtb_scene_set_samples.argtypes = [vp, vp, C.c_uint32]
+        L.rtb_scene_set_materials.argtypes = [vp, vp]
         L.rtb_render.argtypes = [vp, vp, vp, vp]
         L.rtb_render_device.argtypes = [vp, vp, vp, vp]
         L.rtb_render_pixels.argtypes = [vp, vp, vp, C.c_uint64, vp, vp, vp, vp, vp, vp]
@@ -215,6 +216,16 @@ class Scene:
         s = np.ascontiguousarray(samples, np.float32).reshape(-1, 2)
         _check(lib().rtb_scene_set_samples(self._h, _ptr(s), s.shape[0]))
         self._samples = s
+
+    def set_materials(self, ks_ns):
+        """Phong extension (rtb_scene_set_materials): (n_tris,4) {Ks.rgb, Ns} or None for the reference's Lambert."""
+        if ks_ns is None:
+            _check(lib().rtb_scene_set_materials(self._h, None))
+            return
+        k = np.ascontiguousarray(ks_ns, np.float32).reshape(-1, 4)
+        if k.shape[0] != self.info()["n_tris"]:
+            raise ValueError("ks_ns needs one row per primitive")
+        _check(lib().rtb_scene_set_materials(self._h, _ptr(k)))
 
     @staticmethod
     def params(width=1920, height=1080, nb_ray=1, nb_light_sample=100, eye=DEFAULT_CAMERA["eye"],

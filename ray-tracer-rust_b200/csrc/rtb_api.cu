@@ -42,6 +42,7 @@ struct rtb_scene {
     uint32_t n_tris;
     float light[9];
     float4 *d_tris, *d_colors4, *d_nodes;
+    float4* d_ksns;                              // {Ks.rgb, Ns} per primitive (rtb_scene_set_materials), nullptr = Lambert only
     int32_t root;
     RtbBuildInfo info;
     float2* d_samples; uint32_t n_samples;
@@ -146,7 +147,7 @@ void rtb_scene_destroy(rtb_scene* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     cudaFree(s->d_tris); cudaFree(s->d_colors4); cudaFree(s->d_nodes); cudaFree(s->d_samples); cudaFree(s->d_light_pts); cudaFree(s->d_light_perm); cudaFree(s->d_light_gbox);
-    cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame); cudaFree(s->d_cdiv_bad);
+    cudaFree(s->d_counters); cudaFree(s->d_light_box); cudaFree(s->d_frame); cudaFree(s->d_cdiv_bad); cudaFree(s->d_ksns);
     for (int k = 0; k < 2; ++k) {
         rtb_scene::WaveBufs& b = s->wb[k];
         cudaFree(b.d_records); cudaFree(b.d_items); cudaFree(b.d_masks); cudaFree(b.d_queue_ctl);
@@ -244,6 +245,16 @@ cleanup:
 #undef TRY_
 }
 
+int rtb_scene_set_materials(rtb_scene* s, const float* ks_ns) {
+    if (!s) return fail(RTB_ERR_ARG, "rtb_scene_set_materials: null scene");
+    CUDA_TRY(cudaSetDevice(s->device));
+    if (!ks_ns || s->n_tris == 0) { cudaFree(s->d_ksns); s->d_ksns = nullptr; return RTB_OK; }
+    if (!s->d_ksns) CUDA_TRY(cudaMalloc(&s->d_ksns, (size_t)s->n_tris * sizeof(float4)));
+    CUDA_TRY(cudaMemcpyAsync(s->d_ksns, ks_ns, (size_t)s->n_tris * sizeof(float4), cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    return RTB_OK;
+}
+
 int rtb_scene_get_info(const rtb_scene* s, rtb_scene_info* info) {
     if (!s || !info) return fail(RTB_ERR_ARG, "rtb_scene_get_info: null argument");
     info->n_tris = s->n_tris; info->n_nodes = s->info.n_nodes; info->max_depth = s->info.max_depth;
@@ -325,7 +336,7 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
     memset(a, 0, sizeof(*a));
-    a->tris = s->d_tris; a->colors = s->d_colors4; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_pairs = s->d_light_pts + need; a->light_box = s->d_light_box;
+    a->tris = s->d_tris; a->colors = s->d_colors4; a->ksns = s->d_ksns; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_pairs = s->d_light_pts + need; a->light_box = s->d_light_box;
     a->light_perm = use_perm ? s->d_light_perm : nullptr;
     a->light_gbox = s->d_light_gbox; a->n_groups = n_groups; a->group_size = group_size;
     if (s->shadow_mode != 1 && s->grid.valid && s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need) {
@@ -454,7 +465,7 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
     // Only where nothing else hides the stragglers: with several chunks the other worker stream fills the SMs a few long-running
     // bunny warps leave idle, and the term kernel is then extra work (4K/16spp on one GPU: 17.7 ms without, 17.9 ms with); a
     // single-chunk render -- a band share on 8 GPUs, a small frame, a pixel list -- ends on those warps (k_shade 1.15 -> 0.94 ms).
-    const bool use_terms = s->term_mode == 1 || (s->term_mode == 0 && n_chunks == 1);
+    const bool use_terms = (s->term_mode == 1 || (s->term_mode == 0 && n_chunks == 1)) && !a.ksns;     // the specular extension lives in k_shade's general loop only
     if (a.nb_ray && a.nb_light_sample && s->term_bytes && use_terms) {
         term_slots = s->term_bytes / (term_slot_floats * sizeof(float));
         if (term_slots > npp_max * per_pixel / 32) term_slots = npp_max * per_pixel / 32;

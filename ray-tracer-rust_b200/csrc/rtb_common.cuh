@@ -97,6 +97,7 @@ struct RtbGrid {                   // host-side owner of the light grids of one 
 struct TraceArgs {
     const float4* __restrict__ tris;     // 3 float4 per primitive: {v0,n.x} {v1,n.y} {v2,n.z}
     const float4* __restrict__ colors;   // 1 float4 per primitive: {r,g,b, tie_rank as int bits}
+    const float4* __restrict__ ksns;     // {Ks.rgb, Ns} per primitive: Phong specular extension; nullptr = the reference's Lambert
     const float4* __restrict__ nodes;    // 4 float4 per inner node (layout in rtb_bvh.cu)
     const float2* __restrict__ samples;  // n_samples (u,v) pairs
     const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table

@@ -20,6 +20,7 @@ int main(int argc, char** argv) {
     uint64_t seed = 0x5EED0001ull;
     int device = 0;
     std::string out = "output.png";
+    bool use_phong = false;                      // --phong: --mtl + the specular term Ks max(0, r.v)^Ns (rtb_scene_set_materials; extension)
     bool use_mtl = false;                        // --mtl: robust OBJ reader + Kd colours from the .mtl (extension; the reference skips materials)
     std::vector<std::string> objs;
     for (int i = 1; i < argc; ++i) {
@@ -37,14 +38,15 @@ int main(int argc, char** argv) {
         else if (a == "--device") device = atoi(need("--device"));
         else if (a == "--out") out = need("--out");
         else if (a == "--mtl") use_mtl = true;
+        else if (a == "--phong") { use_mtl = true; use_phong = true; }
         else objs.push_back(a);
     }
 
     printf("Building scene\n");                  // src/main.rs:322
-    std::vector<float> verts, colors;
+    std::vector<float> verts, colors, mats;
     for (const std::string& path : objs) {
-        float* v = nullptr; float* kd = nullptr; uint32_t n = 0;
-        int rc = use_mtl ? rtb_import_obj_ex(path.c_str(), RTB_OBJ_MTL, &v, &kd, nullptr, &n) : rtb_import_obj(path.c_str(), &v, &n);
+        float* v = nullptr; float* kd = nullptr; float* ksns = nullptr; uint32_t n = 0;
+        int rc = use_mtl ? rtb_import_obj_ex(path.c_str(), RTB_OBJ_MTL, &v, &kd, use_phong ? &ksns : nullptr, &n) : rtb_import_obj(path.c_str(), &v, &n);
         if (rc != RTB_OK) {
             if (n == 0 && strncmp(rtb_last_error(), "Not a valid path", 16) == 0) { printf("%s\n", rtb_last_error()); continue; }
             fprintf(stderr, "%s\n", rtb_last_error());
@@ -53,7 +55,8 @@ int main(int argc, char** argv) {
         verts.insert(verts.end(), v, v + (size_t)n * 9);
         if (kd) colors.insert(colors.end(), kd, kd + (size_t)n * 3);
         else for (uint32_t k = 0; k < n; ++k) { colors.push_back(1.0f); colors.push_back(1.0f); colors.push_back(1.0f); }   // :143
-        rtb_free(v); rtb_free(kd);
+        if (ksns) mats.insert(mats.end(), ksns, ksns + (size_t)n * 4);
+        rtb_free(v); rtb_free(kd); rtb_free(ksns);
     }
     const float ground[9] = {-10000.0f, 0.0f, -10000.0f, 10000.0f, 0.0f, -10000.0f, 0.0f, 0.0f, 10000.0f};   // :102-111
     verts.insert(verts.end(), ground, ground + 9);
@@ -68,6 +71,10 @@ int main(int argc, char** argv) {
     rtb_scene* scene = nullptr;
     if (rtb_scene_create(&desc, &scene) != RTB_OK) { fprintf(stderr, "%s\n", rtb_last_error()); return 1; }
 
+    if (use_phong) {
+        mats.resize((size_t)desc.n_tris * 4, 0.0f);                                                        // the ground: no highlight
+        if (rtb_scene_set_materials(scene, mats.data()) != RTB_OK) { fprintf(stderr, "%s\n", rtb_last_error()); return 1; }
+    }
     std::vector<float> samples((size_t)n_samples * 2);
     rtb_fill_samples(seed, n_samples, samples.data());
     if (rtb_scene_set_samples(scene, samples.data(), n_samples) != RTB_OK) { fprintf(stderr, "%s\n", rtb_last_error()); return 1; }

@@ -51,6 +51,7 @@ extern "C" {
     pub fn rtb_scene_create(desc: *const RtbSceneDesc, out: *mut *mut RtbScene) -> i32;
     pub fn rtb_scene_destroy(scene: *mut RtbScene);
     pub fn rtb_scene_get_info(scene: *const RtbScene, info: *mut RtbSceneInfo) -> i32;
+    pub fn rtb_scene_set_materials(scene: *mut RtbScene, ks_ns: *const f32) -> i32;
     pub fn rtb_scene_set_samples(scene: *mut RtbScene, samples: *const f32, n_pairs: u32) -> i32;
     pub fn rtb_render(scene: *mut RtbScene, params: *const RtbRenderParams, rgb8: *mut u8, stats: *mut RtbStats) -> i32;
     pub fn rtb_render_device(scene: *mut RtbScene, params: *const RtbRenderParams, d_rgb8: *mut c_void, cuda_stream: *mut c_void) -> i32;

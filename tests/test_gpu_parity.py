@@ -414,3 +414,43 @@ def test_term_wavefront_equals_in_kernel_loops(rtb, big_bunny_inputs, monkeypatc
             for k in ("primary_hits", "shadow_rays", "shadow_occluded"):
                 assert st[k] == stats[0][k], k
         assert stats[1]["launches"] == stats[0]["launches"] + 1
+
+
+@pytest.mark.gpu
+def test_phong_extension_against_cpu_restatement(rtb, big_bunny_inputs, oracle_big_bunny):
+    """SURVEY 8f-1 (an extension: the reference reads no materials and has no specular term): with rtb_scene_set_materials the
+    lit term becomes (c |n.l| + Ks max(0, r.v)^Ns) / denom.  Ks = 0 must give the default path's pixels bit for bit; with the
+    shipped material (models/big_bunny.mtl: Kd 0.8, Ks 0.8, Ns 0) and with a sharper made-up one the CUDA path must agree with
+    the CPU restatement: hit masks identical, >= 99.9 % of the 8-bit channels within +-1 (powf differs by ulps), none by > 2."""
+    v, c, smp = big_bunny_inputs
+    import os
+    _, kd, ksns = rtb.import_obj_ex(os.path.join(S.MODELS, "big_bunny.obj"), mtl=True)
+    n = v.shape[0]
+    kw = dict(width=480, height=270, distance=72.0, nb_ray=2, nb_light_sample=12)
+    sc = rtb.Scene(v, c); sc.set_samples(smp)
+    base, st0 = sc.render(**kw)
+    sc.set_materials(np.zeros((n, 4), np.float32))
+    zero, _ = sc.render(**kw)
+    assert (zero == base).all()
+    pix = S.stratified_pixels(480, 270, 3, seed=5)
+    for ks, ns in ((0.8, 0.0), (0.6, 24.0)):
+        mats = np.zeros((n, 4), np.float32)
+        mats[: n - 1] = [ks, ks, ks, ns]; mats[n - 1] = [0.25, 0.25, 0.25, 8.0]        # the ground gets a dull highlight
+        cols = c.copy(); cols[: n - 1] = kd[0]                                           # Kd from the .mtl
+        scm = rtb.Scene(v, cols); scm.set_samples(smp); scm.set_materials(mats)
+        osc = O.OracleScene(v, cols, True); osc.set_materials(mats)
+        g = scm.render_pixels(pix, **kw)
+        o = osc.render(480, 270, smp, S.EYE, S.LOOK_AT, S.UP, 72.0, S.LIGHT, nb_ray=2, nb_light_sample=12, pixels=pix)
+        assert (g["hit_count"] == o["hit_count"]).all() and (g["prim0"] == o["prim0"]).all()
+        assert g["stats"]["shadow_occluded"] == o["stats"]["shadow_occluded"]
+        d = np.abs(g["rgb8"].astype(np.int32) - o["rgb8"].astype(np.int32))
+        assert (d <= 1).mean() >= 0.999 and d.max() <= 2, (float((d <= 1).mean()), int(d.max()))
+        assert np.allclose(g["rgb_lin"], o["rgb_lin"], rtol=2e-5, atol=1e-7)
+        frame, _ = scm.render(**kw)
+        assert (frame[pix[:, 1], pix[:, 0]] == g["rgb8"]).all()
+        assert (frame != base).any()                                                     # the highlight is there
+        scm.set_materials(None)
+        back, _ = scm.render(**kw)
+        osc.set_materials(None)
+        o2 = osc.render(480, 270, smp, S.EYE, S.LOOK_AT, S.UP, 72.0, S.LIGHT, nb_ray=2, nb_light_sample=12, pixels=pix)
+        assert (back[pix[:, 1], pix[:, 0]] == o2["rgb8"]).all()
