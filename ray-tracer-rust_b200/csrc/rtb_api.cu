@@ -453,6 +453,7 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
     if (npp_max * per_pixel >= 0x7fffffffull)
         return fail(RTB_ERR_LIMIT, "render: one tile row needs %llu rays, above the 2^31 record index", (unsigned long long)(npp_max * per_pixel));
     a.mask_words = (a.nb_light_sample + 31) / 32;
+    a.magic_tiles_x = rtb_magic(a.tiles_x); a.magic_band_rows = rtb_magic(a.band_rows); a.magic_n_samples = rtb_magic(a.n_samples);
     const uint64_t n_chunks = (units_total + units_per_chunk - 1) / units_per_chunk;
     // timed (per-kernel events) or a single chunk: everything on the caller's stream with buffer set 0.  Otherwise chunk c
     // runs on worker stream c & 1 with buffer set c & 1; the workers start after the caller's stream and it waits for them.

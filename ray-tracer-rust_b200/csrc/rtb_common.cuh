@@ -137,6 +137,7 @@ struct TraceArgs {
     uint4* term_tiles;                   // per slot: {first padded pixel of the tile, r, lanes with such a hit point, -}
     float* terms;                        // [slot][channel < term_channels][lane][sample, row stride term_stride]; nullptr: off
     uint32_t term_cap, term_stride, term_channels;   // slots available; floats per row (multiple of 4); 1 (all colours grey) or 3
+    uint32_t magic_tiles_x, magic_band_rows, magic_n_samples;   // rtb_magic(): floor(2^32 / d) for the three runtime divisors of pixel_of / primary_dir
     uint32_t n_pix_padded, tiles_x, mask_words;   // n_pix_padded: record stride of THIS chunk (multiple of 256)
     uint32_t pix_base, n_pix_chunk;      // chunk = padded pixel indices [pix_base, pix_base + n_pix_chunk)
     // outputs
@@ -146,6 +147,19 @@ struct TraceArgs {
     float* out_rgb_lin; uint8_t* out_hit_count; int32_t* out_prim0; float* out_t0;
     unsigned long long* counters;        // [0] primary hits [1] shadow rays [2] occluded [3] box tests [4] tri tests [5] stack overflow
 };
+
+// n / d for a runtime divisor without the integer-division sequence: with m = floor(2^32 / d) (0xffffffff for d = 1),
+// mulhi(n, m) is floor(n / d) or one less for every 32-bit n; one compare fixes it.  rem receives n % d.
+static inline uint32_t rtb_magic(uint32_t d) { return d <= 1u ? 0xffffffffu : (uint32_t)(0x100000000ull / d); }
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t rtb_udiv(uint32_t n, uint32_t d, uint32_t magic, uint32_t& rem) {
+    uint32_t q = __umulhi(n, magic);
+    uint32_t r = n - q * d;
+    if (r >= d) { ++q; r -= d; }
+    rem = r;
+    return q;
+}
+#endif
 
 #define RTB_CTR_PRIMARY_HITS 0
 #define RTB_CTR_SHADOW 1
