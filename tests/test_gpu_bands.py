@@ -125,3 +125,27 @@ def test_render_into_pinned_host_rows_chunk_by_chunk(built, big_bunny_inputs, mo
         pinned = torch.zeros(want.size, dtype=torch.uint8).pin_memory()
         got, _ = sc.render(out=pinned.numpy().reshape(want.shape), **kw)
         assert (got == want).all()
+
+
+def test_full_size_4k_16spp_band_shares_tile_the_frame(scene):
+    """BASELINE config 3 at its full size (3840x2160, 16 rays/pixel, 100 light samples): the 8 band shares of the bench
+    (4-row bands; each a single chunk, so the term wavefront runs) must tile the full frame (8 chunks on two streams, k_shade's
+    own loops) byte for byte, with the same ray counts -- a size-independent property; the oracle comparison of this config
+    is test_gpu_parity.py::test_4k_16spp_subset_exact."""
+    D = importlib.import_module("ray_tracer_rust_b200.distributed")
+    kw = dict(width=3840, height=2160, nb_ray=16, nb_light_sample=100)
+    full, st_full = scene.render(**kw)
+    assert st_full["launches"] >= 8 * 3
+    parts, sums = [], {"primary_hits": 0, "shadow_rays": 0, "shadow_occluded": 0}
+    for r in range(8):
+        rows, st = scene.render(band_rows=4, rank=r, world=8, **kw)
+        parts.append(rows)
+        for k in sums:
+            sums[k] += st[k]
+    for k in sums:
+        assert sums[k] == st_full[k], k
+    assert (D.assemble_on_host(parts, 3840, 2160, 4, 8) == full).all()
+    # pixels of the frame against the per-pixel entry point (the one the oracle tests use)
+    pix = S.stratified_pixels(3840, 2160, 97, seed=21)
+    g = scene.render_pixels(pix, **kw)
+    assert (full[pix[:, 1], pix[:, 0]] == g["rgb8"]).all()
