@@ -166,3 +166,21 @@ def test_import_obj_ex_robust_syntax(rtb, tmp_path):
             rtb.import_obj_ex(str(q))
     with pytest.raises(rtb.RtbError):
         rtb.import_obj_ex(str(tmp_path / "missing.obj"))
+
+
+def test_reciprocal_integer_division_rule():
+    """csrc/rtb_common.cuh rtb_magic / rtb_udiv (tile / tiles_x, row / band_rows, % n_samples in the kernels): with
+    m = floor(2^32 / d) (0xffffffff for d = 1), mulhi(n, m) is floor(n / d) or one less for every 32-bit n, so one fix-up
+    gives the exact quotient and remainder.  Restated in numpy on edge and random operands."""
+    rng = np.random.default_rng(5)
+    ds = np.concatenate([np.array([1, 2, 3, 5, 7, 8, 240, 480, 7919, 2000000, 2**31 - 1, 2**31, 2**32 - 1], np.uint64),
+                         rng.integers(1, 2**32, 200, dtype=np.uint64)])
+    ns = np.concatenate([np.array([0, 1, 2, 2**16, 2**24 - 1, 2**31, 2**32 - 2, 2**32 - 1], np.uint64),
+                         rng.integers(0, 2**32, 5000, dtype=np.uint64)])
+    for d in ds:
+        m = np.uint64(0xffffffff) if d <= 1 else np.uint64(2**32) // d
+        q = (ns * m) >> np.uint64(32)
+        r = ns - q * d
+        fix = r >= d
+        q = q + fix.astype(np.uint64); r = r - d * fix.astype(np.uint64)
+        assert (q == ns // d).all() and (r == ns % d).all(), int(d)
