@@ -50,6 +50,25 @@ typedef struct {
 
 #define RTB_TIE_RANK_MAX_TRIS 65536u
 
+/* Tunables of a scene (all optional: pass NULL to rtb_scene_create_ex, or leave a field 0, for the default).  They were
+ * environment variables in round 1; the variables (named beside each field) are still read and OVERRIDE the struct, for
+ * experiments only. */
+typedef struct {
+    uint32_t struct_size;         /* sizeof(rtb_scene_options), so that the struct can grow */
+    int32_t shadow_mode;          /* 0 auto: light grids when they apply; 1 candidate lists / BVH walks only; 2 = 0   RTB200_SHADOW=lists|grid */
+    int32_t primary_mode;         /* 0 auto: camera grid when it applies; 1 BVH traversal only                       RTB200_PRIMARY=bvh */
+    int32_t term_mode;            /* 0 auto (single-chunk renders); 1 always; -1 never: the term wavefront             RTB200_TERMS=1|0 */
+    uint64_t chunk_rays;          /* rays per wavefront chunk, 0 = 16 Mi                                               RTB200_CHUNK_RAYS */
+    uint64_t term_bytes;          /* memory per buffer set of the term wavefront, 0 = 1 GiB, UINT64_MAX = none         RTB200_TERM_MB */
+    uint64_t grid_entry_cap;      /* light / camera grid entries above which the list / walk path is taken, 0 = 512 Mi */
+    float grid_cell_factor;       /* light-grid cell size / log-mean primitive extent, 0 = 0.25                        RTB200_GRID_CELL */
+    float cam_cell_px;            /* camera-grid cell size in pixels, 0 = 2                                            RTB200_CAM_CELL */
+    int32_t cdiv_off;             /* 1: never the two-operation division by denom                                      RTB200_CDIV=0 */
+    int32_t trace_chunks;         /* 1: per-chunk kernel times of profiled renders on stderr                           RTB200_TRACE_CHUNKS */
+    int32_t shadow_kernel;        /* 0 = 2: k_shadow_grid2 (ray table + queues in shared memory); 1: k_shadow_grid      RTB200_SHADOW_KERNEL */
+    int32_t primary_kernel;       /* 0 = 2: k_primary2 (thread per pixel, loop over its rays); 1: k_primary            RTB200_PRIMARY_KERNEL */
+} rtb_scene_options;
+
 /* Per-frame parameters: the compile-time constants of src/main.rs:38-40 and the literals of
  * src/main.rs:349-356 made explicit, plus the multi-GPU band ownership. */
 typedef struct {
@@ -67,35 +86,52 @@ typedef struct {
 #define RTB_FLAG_COUNTERS 1u      /* also count AABB / triangle tests (slower instrumented kernel) */
 #define RTB_FLAG_PROFILE 2u       /* per-kernel times in rtb_stats: the chunks of the frame run one after the other on one stream
                                      instead of overlapping on two (a little slower) */
-#define RTB_FLAG_FRAME_ROWS 4u    /* rtb_render_device only: d_rgb8 is the FULL frame (height * width * 3 bytes) and every owned row is
-                                     written at its own position in it, not compactly.  With d_rgb8 = rank 0's frame mapped into this
+#define RTB_FLAG_FRAME_ROWS 4u    /* the output buffer is the FULL frame (height * width * 3 bytes) and every owned row is written at its
+                                     own position in it, not compactly.  rtb_render_device: with d_rgb8 = rank 0's frame mapped into this
                                      process (rtb_peer_open) the shading kernel stores its pixels straight into the gathered frame over
-                                     NVLink: render and gather are one kernel, no staging buffer, no placement pass. */
+                                     NVLink: render and gather are one kernel, no staging buffer, no placement pass.  rtb_render: the HOST
+                                     buffer is the full frame (e.g. one pinned allocation shared by all ranks) and each chunk's rows are
+                                     copied device-to-host straight to their rows of it (strided copies, one per chunk). */
+#define RTB_FLAG_GATHER_PEER 8u   /* rtb_render_multi only: devices 1.. store their rows into device 0's frame over NVLink peer access
+                                     (RTB_FLAG_FRAME_ROWS) and ONE device-to-host copy follows; default: every device copies its own
+                                     rows straight into the caller's host frame over its own PCIe link. */
 
 typedef struct {
     uint64_t primary_rays, primary_hits, shadow_rays, shadow_occluded;
     uint64_t box_tests, tri_tests;   /* only with RTB_FLAG_COUNTERS, else 0 */
     float kernel_ms;                 /* device time of the trace kernels of this call (CUDA events) */
     uint32_t launches;               /* kernels launched by this call */
-    float primary_ms, shadow_ms, shade_ms;   /* k_primary / k_shadow_plan + k_shadow_lists + k_shadow_queue / k_shade; only with
-                                                RTB_FLAG_PROFILE, else 0 */
+    float primary_ms, shadow_ms, shade_ms;   /* k_primary / the shadow kernel(s) (k_shadow_grid on the light-grid path; k_shadow_plan +
+                                                k_shadow_lists + k_shadow_queue on the list / walk path) / k_shade (+ k_shade_terms);
+                                                only with RTB_FLAG_PROFILE, else 0 */
     uint32_t queued_hits;            /* hit points whose shadow rays needed the BVH (shadow queue length) */
     uint32_t queued_groups;          /* (hit point, light-sample group) pairs left after the per-group bundle test */
     uint32_t queued_walks;           /* ... of which need a per-ray BVH walk (not just a short candidate list) */
     uint32_t grid_cells, grid_entries, grid_big;   /* light grids in use for this call (0 = list / walk path): cells, entries,
                                                       primitives outside the grids */
     float grid_build_ms;             /* device time of the last grid build (once per sample table, not per frame) */
+    uint32_t grid_rebuilds;          /* light- or camera-grid builds this call enqueued (0: both cached) ... */
+    uint32_t grid_redo;              /* ... of which failed their device-side capacity check: the frame was rendered a second time
+                                        after a synchronous rebuild (see rtb_render) */
 } rtb_stats;
 
 typedef struct {
     uint32_t n_tris, n_nodes, max_depth, ploc_iterations;
     float sah_cost;                  /* surface-area-heuristic cost of the built tree (diagnostic) */
     float build_ms;
+    uint32_t tie_mode;               /* how exact equal-distance ties are broken: RTB_TIE_REFERENCE (the reference's leaf order,
+                                        replayed on the device), RTB_TIE_CALLER (rtb_scene_desc.tie_rank) or RTB_TIE_INDEX (larger
+                                        primitive index: scenes above RTB_TIE_RANK_MAX_TRIS primitives -- on exact ties such a
+                                        scene may differ from the reference's tree order) */
 } rtb_scene_info;
+#define RTB_TIE_REFERENCE 0u
+#define RTB_TIE_CALLER 1u
+#define RTB_TIE_INDEX 2u
 
 /* --- replaces BoundingVolumeHierarchy::new + Scene{..} (src/main.rs:349-358): uploads the
  *     primitives, flattens them to SoA float4, builds the BVH on the device. */
 int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out);
+int rtb_scene_create_ex(const rtb_scene_desc* desc, const rtb_scene_options* options, rtb_scene** out);
 void rtb_scene_destroy(rtb_scene* scene);
 int rtb_scene_get_info(const rtb_scene* scene, rtb_scene_info* info);
 
@@ -111,11 +147,57 @@ int rtb_scene_set_materials(rtb_scene* scene, const float* ks_ns);
  *     because the reference draws it from an OS-seeded RNG. */
 int rtb_scene_set_samples(rtb_scene* scene, const float* samples, uint32_t n_pairs);
 
+/* Same table, uploaded asynchronously: `samples` must be PINNED host memory (cudaHostAlloc / cudaHostRegister; pageable memory
+ * falls back to rtb_scene_set_samples) and must stay valid and unchanged until the next render call on this scene has returned.
+ * Returns at once.  The first entries (the only ones the light points and the light grids depend on) go first on the scene's
+ * stream, the rest follows on a copy stream while the next render rebuilds the light grids; the primary-ray kernel waits for it. */
+int rtb_scene_set_samples_async(rtb_scene* scene, const float* samples, uint32_t n_pairs);
+
 /* --- replaces render(scene) up to (not including) the PNG save (src/main.rs:242-310):
  *     renders the rows owned by (rank, world) and copies them to the HOST buffer rgb8
  *     (rtb_owned_rows(...) * width * 3 bytes, row-major RGB8, bands in increasing order).
  *     Blocking.  stats may be NULL. */
 int rtb_render(rtb_scene* scene, const rtb_render_params* params, uint8_t* rgb8, rtb_stats* stats);
+
+/* render() on several GPUs of one box from ONE host thread's point of view (the reference's render fans out to its worker threads
+ * and joins them itself, src/main.rs:269-303): scenes[i] is the same scene created on device i (rtb_scene_desc.device), all with the
+ * same sample table (rtb_scene_set_samples[_async] on each, or rtb_scenes_set_samples).  Band b of params->band_rows rows (0 = 4)
+ * is rendered by scenes[b % n_gpus] (params->rank / world are ignored); one host thread per device runs inside the call and every
+ * device copies its finished rows straight to their place in rgb8, the full HOST frame (height * width * 3; pinned memory makes
+ * the copies asynchronous).  With RTB_FLAG_GATHER_PEER the rows travel over NVLink into scenes[0]'s device frame instead and one
+ * device-to-host copy follows.  Blocking.  stats (may be NULL) = sums over the devices, times = the slowest device.
+ * The bytes equal those of rtb_render on one GPU. */
+int rtb_render_multi(rtb_scene* const* scenes, uint32_t n_gpus, const rtb_render_params* params, uint8_t* rgb8, rtb_stats* stats);
+int rtb_scenes_set_samples(rtb_scene* const* scenes, uint32_t n_gpus, const float* samples, uint32_t n_pairs);
+
+/* Frame sequence (replaces calling render() + img.save per pose, src/main.rs:242-317): renders n_poses frames that
+ * differ only in the camera.  Scene, BVH, sample table and light grids stay resident; the camera grid is rebuilt per pose without
+ * host synchronisation; frames alternate between two device / pinned host buffers so that the device-to-host copy and the
+ * consumer of frame k overlap the kernels of frame k + 1.  Per finished frame, in pose order:
+ *   frames != NULL: the frame is copied to frames + k * height * width * 3 (HOST);
+ *   png_pattern != NULL: a printf pattern with one %u (e.g. "frame_%04u.png"), the frame is encoded and written by a pool of host
+ *     threads that runs alongside the rendering (img.save, src/main.rs:312-315);
+ *   on_frame != NULL: called from the consumer thread with the pinned host frame (valid during the call).
+ * params->rank / world / band_rows select band ownership as in rtb_render (world <= 1: whole frames).  Blocking; stats may be NULL. */
+typedef struct { float eye[3], look_at[3], up[3], distance; } rtb_camera_pose;
+typedef void (*rtb_frame_fn)(void* user, uint32_t pose_index, const uint8_t* rgb8, uint32_t width, uint32_t rows);
+typedef struct {
+    double seconds;                  /* wall time of the whole call */
+    float device_ms;                 /* device time from the first kernel to the last copy (CUDA events) */
+    uint32_t frames, cam_grid_redo;  /* frames delivered; poses whose speculative camera-grid build had to be redone */
+    uint64_t primary_rays, shadow_rays;
+} rtb_sequence_stats;
+int rtb_render_sequence(rtb_scene* scene, const rtb_render_params* params, const rtb_camera_pose* poses, uint32_t n_poses,
+                        uint8_t* frames, const char* png_pattern, rtb_frame_fn on_frame, void* user, rtb_sequence_stats* stats);
+/* The same over several GPUs, frame-parallel: pose k is rendered whole by scenes[k % n_gpus] (replicas, no exchange); outputs as
+ * above, delivered per device in pose order. */
+int rtb_render_sequence_multi(rtb_scene* const* scenes, uint32_t n_gpus, const rtb_render_params* params, const rtb_camera_pose* poses,
+                              uint32_t n_poses, uint8_t* frames, const char* png_pattern, rtb_sequence_stats* stats);
+
+/* Roofline denominators measured on the device: k_fp32_peak (independent FFMA chains on every SM: FP32 TFLOP/s with
+ * FMA = 2 flop), k_l2_peak (read-only sweep of a 32 MiB buffer by all SMs, 128-bit loads: GB/s) and the same sweep over 2 GiB
+ * (HBM read GB/s).  Any output may be NULL. */
+int rtb_measure_peaks(int32_t device, float* fp32_tflops, float* l2_read_gbs, float* hbm_read_gbs);
 
 /* Same, but the output stays on the device: d_rgb8 is a device pointer on the scene's device,
  * cuda_stream a cudaStream_t (NULL = default stream).  Asynchronous: returns after the launch.

@@ -16,6 +16,8 @@ LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(_HERE, "librtb200.so")  
 RTB_FLAG_COUNTERS = 1
 RTB_FLAG_PROFILE = 2
 RTB_FLAG_FRAME_ROWS = 4
+RTB_FLAG_GATHER_PEER = 8
+RTB_TIE_REFERENCE, RTB_TIE_CALLER, RTB_TIE_INDEX = 0, 1, 2
 
 
 class RtbError(RuntimeError):
@@ -38,7 +40,8 @@ class Stats(C.Structure):
                 ("shadow_occluded", C.c_uint64), ("box_tests", C.c_uint64), ("tri_tests", C.c_uint64),
                 ("kernel_ms", C.c_float), ("launches", C.c_uint32), ("primary_ms", C.c_float), ("shadow_ms", C.c_float),
                 ("shade_ms", C.c_float), ("queued_hits", C.c_uint32), ("queued_groups", C.c_uint32), ("queued_walks", C.c_uint32),
-                ("grid_cells", C.c_uint32), ("grid_entries", C.c_uint32), ("grid_big", C.c_uint32), ("grid_build_ms", C.c_float)]
+                ("grid_cells", C.c_uint32), ("grid_entries", C.c_uint32), ("grid_big", C.c_uint32), ("grid_build_ms", C.c_float),
+                ("grid_rebuilds", C.c_uint32), ("grid_redo", C.c_uint32)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -46,10 +49,31 @@ class Stats(C.Structure):
 
 class SceneInfo(C.Structure):
     _fields_ = [("n_tris", C.c_uint32), ("n_nodes", C.c_uint32), ("max_depth", C.c_uint32), ("ploc_iterations", C.c_uint32),
-                ("sah_cost", C.c_float), ("build_ms", C.c_float)]
+                ("sah_cost", C.c_float), ("build_ms", C.c_float), ("tie_mode", C.c_uint32)]
 
 
-EXPORTS = ["rtb_scene_create", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render",
+class SceneOptions(C.Structure):
+    """rtb_scene_options: the tunables that were environment variables (0 = default)."""
+    _fields_ = [("struct_size", C.c_uint32), ("shadow_mode", C.c_int32), ("primary_mode", C.c_int32), ("term_mode", C.c_int32),
+                ("chunk_rays", C.c_uint64), ("term_bytes", C.c_uint64), ("grid_entry_cap", C.c_uint64),
+                ("grid_cell_factor", C.c_float), ("cam_cell_px", C.c_float), ("cdiv_off", C.c_int32), ("trace_chunks", C.c_int32),
+                ("shadow_kernel", C.c_int32), ("primary_kernel", C.c_int32)]
+
+
+class CameraPose(C.Structure):
+    _fields_ = [("eye", C.c_float * 3), ("look_at", C.c_float * 3), ("up", C.c_float * 3), ("distance", C.c_float)]
+
+
+class SequenceStats(C.Structure):
+    _fields_ = [("seconds", C.c_double), ("device_ms", C.c_float), ("frames", C.c_uint32), ("cam_grid_redo", C.c_uint32),
+                ("primary_rays", C.c_uint64), ("shadow_rays", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+EXPORTS = ["rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
+           "rtb_render_sequence", "rtb_render_sequence_multi", "rtb_measure_peaks", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render",
            "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj", "rtb_import_obj_ex",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
 
@@ -66,6 +90,13 @@ def lib():
         L = C.CDLL(LIB_PATH)
         vp = C.c_void_p
         L.rtb_scene_create.argtypes = [vp, vp]
+        L.rtb_scene_create_ex.argtypes = [vp, vp, vp]
+        L.rtb_scene_set_samples_async.argtypes = [vp, vp, C.c_uint32]
+        L.rtb_scenes_set_samples.argtypes = [vp, C.c_uint32, vp, C.c_uint32]
+        L.rtb_render_multi.argtypes = [vp, C.c_uint32, vp, vp, vp]
+        L.rtb_render_sequence.argtypes = [vp, vp, vp, C.c_uint32, vp, C.c_char_p, vp, vp, vp]
+        L.rtb_render_sequence_multi.argtypes = [vp, C.c_uint32, vp, vp, C.c_uint32, vp, C.c_char_p, vp]
+        L.rtb_measure_peaks.argtypes = [C.c_int32, vp, vp, vp]
         L.rtb_scene_destroy.argtypes = [vp]; L.rtb_scene_destroy.restype = None
         L.rtb_scene_get_info.argtypes = [vp, vp]
         L.rtb_scene_set_samples.argtypes = [vp, vp, C.c_uint32]
@@ -181,7 +212,7 @@ class Scene:
     """Device-resident Scene{light, camera, bvh} (src/tracer/utils/scene.rs:6-12).  Primitives are given in the
     reference's order: OBJ triangles in argv order, ground last (src/main.rs:324-335)."""
 
-    def __init__(self, verts, colors, light=DEFAULT_LIGHT, device=0, tie_rank=None):
+    def __init__(self, verts, colors, light=DEFAULT_LIGHT, device=0, tie_rank=None, **options):
         self.verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
         self.colors = np.ascontiguousarray(colors, np.float32).reshape(-1, 3)
         if self.verts.shape[0] != self.colors.shape[0]:
@@ -196,7 +227,16 @@ class Scene:
         d.device = device
         self.device = device
         h = C.c_void_p()
-        _check(lib().rtb_scene_create(C.byref(d), C.byref(h)))
+        if options:                                  # rtb_scene_options fields by name (shadow_mode=1, chunk_rays=6000, ...)
+            o = SceneOptions()
+            o.struct_size = C.sizeof(SceneOptions)
+            for k, v in options.items():
+                if k not in dict(SceneOptions._fields_):
+                    raise TypeError("unknown scene option %r" % k)
+                setattr(o, k, v)
+            _check(lib().rtb_scene_create_ex(C.byref(d), C.byref(o), C.byref(h)))
+        else:
+            _check(lib().rtb_scene_create(C.byref(d), C.byref(h)))
         self._h = h
         self._samples = None
 
@@ -216,6 +256,28 @@ class Scene:
         s = np.ascontiguousarray(samples, np.float32).reshape(-1, 2)
         _check(lib().rtb_scene_set_samples(self._h, _ptr(s), s.shape[0]))
         self._samples = s
+
+    def set_samples_async(self, samples):
+        """rtb_scene_set_samples_async: `samples` must be pinned host memory that stays valid until the next render returns."""
+        s = np.ascontiguousarray(samples, np.float32).reshape(-1, 2)
+        _check(lib().rtb_scene_set_samples_async(self._h, _ptr(s), s.shape[0]))
+        self._samples = s
+
+    def render_sequence(self, poses, frames=None, png_pattern=None, **kw):
+        """rtb_render_sequence: poses = [(eye, look_at, up[, distance])]; returns (frames (n, rows, width, 3) uint8, stats)."""
+        p = self.params(**kw)
+        n = len(poses)
+        arr = (CameraPose * max(n, 1))()
+        for k, c in enumerate(poses):
+            arr[k].eye[:] = [float(x) for x in c[0]]; arr[k].look_at[:] = [float(x) for x in c[1]]; arr[k].up[:] = [float(x) for x in c[2]]
+            arr[k].distance = float(c[3]) if len(c) > 3 else p.distance
+        rows = owned_rows(p.height, p.band_rows, p.rank, max(1, p.world))
+        if frames is None and png_pattern is None:
+            frames = np.empty((n, rows, p.width, 3), np.uint8)
+        st = SequenceStats()
+        _check(lib().rtb_render_sequence(self._h, C.byref(p), arr, n, _ptr(frames), os.fsencode(png_pattern) if png_pattern else None,
+                                         None, None, C.byref(st)))
+        return frames, st.as_dict()
 
     def set_materials(self, ks_ns):
         """Phong extension (rtb_scene_set_materials): (n_tris,4) {Ks.rgb, Ns} or None for the reference's Lambert."""
@@ -296,6 +358,56 @@ class Scene:
                                        _ptr(out["hit_count"]), _ptr(out["prim0"]), _ptr(out["t0"]), C.byref(st)))
         out["stats"] = st.as_dict()
         return out
+
+
+def _scene_array(scenes):
+    arr = (C.c_void_p * len(scenes))()
+    for i, sc in enumerate(scenes):
+        arr[i] = sc._h
+    return arr
+
+
+def set_samples_multi(scenes, samples):
+    """rtb_scenes_set_samples: the same table on every scene, uploaded by one host thread per device (pinned memory: async)."""
+    s = np.ascontiguousarray(samples, np.float32).reshape(-1, 2)
+    _check(lib().rtb_scenes_set_samples(_scene_array(scenes), len(scenes), _ptr(s), s.shape[0]))
+    for sc in scenes:
+        sc._samples = s
+
+
+def render_multi(scenes, out=None, gather_peer=False, **kw):
+    """rtb_render_multi: one frame over len(scenes) GPUs (scenes[i] lives on device i) -> ((height, width, 3) uint8, stats)."""
+    p = Scene.params(**kw)
+    if gather_peer:
+        p.flags |= RTB_FLAG_GATHER_PEER
+    if out is None:
+        out = np.empty((p.height, p.width, 3), np.uint8)
+    st = Stats()
+    _check(lib().rtb_render_multi(_scene_array(scenes), len(scenes), C.byref(p), _ptr(out), C.byref(st)))
+    return out, st.as_dict()
+
+
+def render_sequence_multi(scenes, poses, frames=None, png_pattern=None, **kw):
+    """rtb_render_sequence_multi: pose k on scenes[k % n] (frame-parallel) -> ((n, height, width, 3) uint8, stats)."""
+    p = Scene.params(**kw)
+    n = len(poses)
+    arr = (CameraPose * max(n, 1))()
+    for k, c in enumerate(poses):
+        arr[k].eye[:] = [float(x) for x in c[0]]; arr[k].look_at[:] = [float(x) for x in c[1]]; arr[k].up[:] = [float(x) for x in c[2]]
+        arr[k].distance = float(c[3]) if len(c) > 3 else p.distance
+    if frames is None and png_pattern is None:
+        frames = np.empty((n, p.height, p.width, 3), np.uint8)
+    st = SequenceStats()
+    _check(lib().rtb_render_sequence_multi(_scene_array(scenes), len(scenes), C.byref(p), arr, n, _ptr(frames),
+                                           os.fsencode(png_pattern) if png_pattern else None, C.byref(st)))
+    return frames, st.as_dict()
+
+
+def measure_peaks(device=0, hbm=True):
+    """rtb_measure_peaks -> dict(fp32_tflops, l2_read_gbs, hbm_read_gbs): the roofline denominators, measured."""
+    f, l, h = C.c_float(0), C.c_float(0), C.c_float(0)
+    _check(lib().rtb_measure_peaks(device, C.byref(f), C.byref(l), C.byref(h) if hbm else None))
+    return {"fp32_tflops": f.value, "l2_read_gbs": l.value, "hbm_read_gbs": h.value if hbm else None}
 
 
 def deinterleave_bands(device, d_staged, stride_bytes, d_frame, width, height, band_rows, world, stream=0):

@@ -9,7 +9,13 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <deque>
 #include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+#include <chrono>
 
 // launchers / builders defined in the other translation units
 struct RtbBuildInfo { uint32_t n_nodes, max_depth, iterations; float sah_cost, build_ms; };
@@ -17,8 +23,9 @@ cudaError_t rtb_build_scene(const float*, const float*, const int*, uint32_t, fl
 cudaError_t rtb_tie_rank_device(const float4* d_tris, uint32_t n, int* d_rank_out, float4* d_colors4, cudaStream_t st);
 cudaError_t rtb_launch_trace(const TraceArgs&, bool, cudaStream_t, cudaEvent_t*);
 cudaError_t rtb_grid_scene_stats(RtbGrid&, const float4*, uint32_t, cudaStream_t);
-cudaError_t rtb_grid_build(RtbGrid&, const float4*, uint32_t, const float4*, uint32_t, float, cudaStream_t);
-cudaError_t rtb_cam_grid_build(RtbGrid&, const float4*, uint32_t, float4*, float4*, const CameraBasis&, float, cudaStream_t);
+cudaError_t rtb_grid_build(RtbGrid&, const float4*, uint32_t, const float4*, uint32_t, float, bool, cudaStream_t);
+cudaError_t rtb_cam_grid_build(RtbGrid&, const float4*, uint32_t, float4*, float4*, const CameraBasis&, float, bool, cudaStream_t);
+cudaError_t rtb_grid_validate(RtbGrid&, cudaStream_t, bool*);
 void rtb_grid_free(RtbGrid&);
 cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, float*, cudaStream_t);
 cudaError_t rtb_launch_light_groups(const float4*, const float*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint16_t*, float*, cudaStream_t);
@@ -86,6 +93,16 @@ struct rtb_scene {
     bool terms_ran;                              // the last render launched k_shade_terms
     uint64_t term_bytes;                         // RTB200_TERM_MB: memory per buffer set for the term wavefront (default 1 GiB, 0 = off)
     bool cdiv_off;                               // RTB200_CDIV=0: always the three-operation shared-reciprocal division
+    uint32_t tie_mode;                           // RTB_TIE_*
+    uint32_t shadow_kernel, primary_kernel;      // kernel forms (rtb_scene_options / RTB200_SHADOW_KERNEL / RTB200_PRIMARY_KERNEL)
+    // asynchronous sample-table upload (rtb_scene_set_samples_async): the prefix the light tables need travels on `stream`,
+    // the rest on `copy_stream`; renders make their stream wait for ev_prefix / ev_samples where they need the data
+    cudaStream_t copy_stream; cudaEvent_t ev_prefix, ev_samples, ev_idle; bool samples_pending; uint32_t samples_prefix;
+    uint32_t grid_rebuilds, grid_redo;           // grid builds enqueued / redone by the last blocking render
+    // rtb_render_multi with RTB_FLAG_GATHER_PEER: the full frame on this device, written by every device of the call
+    uint8_t* d_full; size_t full_cap;
+    // rtb_render_sequence: two device frames, two pinned host frames, snapshots of the camera grid's control words
+    uint8_t* d_seq[2]; uint8_t* h_seq[2]; size_t seq_cap; uint32_t* h_seq_ctl; cudaEvent_t ev_seq[2], ev_seq0, ev_seq1;
 };
 
 // ---- Color::to_rgba threshold table (color.rs:10-33) ---------------------------------------
@@ -158,6 +175,15 @@ void rtb_scene_destroy(rtb_scene* s) {
     }
     if (s->ev_fork) cudaEventDestroy(s->ev_fork);
     rtb_grid_free(s->grid); rtb_grid_free(s->cam_grid); cudaFree(s->d_cam_tris); cudaFree(s->d_cam_origin);
+    cudaFree(s->d_full);
+    for (int k = 0; k < 2; ++k) { cudaFree(s->d_seq[k]); if (s->h_seq[k]) cudaFreeHost(s->h_seq[k]); if (s->ev_seq[k]) cudaEventDestroy(s->ev_seq[k]); }
+    if (s->h_seq_ctl) cudaFreeHost(s->h_seq_ctl);
+    if (s->ev_seq0) cudaEventDestroy(s->ev_seq0);
+    if (s->ev_seq1) cudaEventDestroy(s->ev_seq1);
+    if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+    if (s->ev_prefix) cudaEventDestroy(s->ev_prefix);
+    if (s->ev_samples) cudaEventDestroy(s->ev_samples);
+    if (s->ev_idle) cudaEventDestroy(s->ev_idle);
     if (s->h_pinned) cudaFreeHost(s->h_pinned);
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -166,8 +192,16 @@ void rtb_scene_destroy(rtb_scene* s) {
     delete s;
 }
 
-int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
+int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) { return rtb_scene_create_ex(desc, nullptr, out); }
+
+int rtb_scene_create_ex(const rtb_scene_desc* desc, const rtb_scene_options* opt_in, rtb_scene** out) {
     if (!desc || !out) return fail(RTB_ERR_ARG, "rtb_scene_create: null argument");
+    rtb_scene_options opt;
+    memset(&opt, 0, sizeof(opt));
+    if (opt_in) {
+        if (opt_in->struct_size == 0 || opt_in->struct_size > sizeof(opt)) return fail(RTB_ERR_ARG, "rtb_scene_create_ex: options.struct_size %u (this library: %zu)", opt_in->struct_size, sizeof(opt));
+        memcpy(&opt, opt_in, opt_in->struct_size);
+    }
     *out = nullptr;
     if (desc->n_tris && (!desc->verts || !desc->colors)) return fail(RTB_ERR_ARG, "rtb_scene_create: null vertex/colour array");
     if (desc->n_tris > 0x3fffffffu) return fail(RTB_ERR_LIMIT, "rtb_scene_create: too many primitives");
@@ -192,21 +226,34 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
     TRY_(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     TRY_(cudaEventCreate(&s->ev0)); TRY_(cudaEventCreate(&s->ev1));
     for (int k = 0; k < 4 * 32; ++k) TRY_(cudaEventCreate(&s->evp[k]));
-    s->chunk_rays = 16ull << 20;
+    // tunables: rtb_scene_options (0 = default), then the environment variables of the same meaning as overrides
+    s->chunk_rays = opt.chunk_rays ? opt.chunk_rays : 16ull << 20;
     if (const char* env = getenv("RTB200_CHUNK_RAYS")) { const long long v = atoll(env); if (v > 0) s->chunk_rays = (uint64_t)v; }
-    s->shadow_mode = 0; s->grid_cell_factor = 0.25f;
+    s->shadow_mode = opt.shadow_mode == 1 ? 1 : 0; s->grid_cell_factor = opt.grid_cell_factor > 0.0f ? opt.grid_cell_factor : 0.25f;
     if (const char* env = getenv("RTB200_SHADOW")) s->shadow_mode = !strcmp(env, "lists") ? 1 : (!strcmp(env, "grid") ? 2 : 0);
+    s->cdiv_off = opt.cdiv_off != 0;
     if (const char* env = getenv("RTB200_CDIV")) s->cdiv_off = atoi(env) == 0;
+    s->term_mode = opt.term_mode > 0 ? 1 : (opt.term_mode < 0 ? -1 : 0);
     if (const char* env = getenv("RTB200_TERMS")) s->term_mode = !strcmp(env, "1") ? 1 : (!strcmp(env, "0") ? -1 : 0);
-    s->term_bytes = 1ull << 30;
+    s->term_bytes = opt.term_bytes == UINT64_MAX ? 0 : (opt.term_bytes ? opt.term_bytes : 1ull << 30);
     if (const char* env = getenv("RTB200_TERM_MB")) { const long long v = atoll(env); if (v >= 0) s->term_bytes = (uint64_t)v << 20; }
+    s->grid.entry_cap_limit = opt.grid_entry_cap; s->cam_grid.entry_cap_limit = opt.grid_entry_cap;
     s->all_grey = true;
     for (uint32_t i = 0; i < desc->n_tris && s->all_grey; ++i)
         s->all_grey = desc->colors[3 * i] == desc->colors[3 * i + 1] && desc->colors[3 * i + 1] == desc->colors[3 * i + 2];
+    s->shadow_kernel = opt.shadow_kernel == 1 ? 1u : 2u; s->primary_kernel = opt.primary_kernel == 1 ? 1u : 2u;
+    if (const char* env = getenv("RTB200_SHADOW_KERNEL")) s->shadow_kernel = atoi(env) == 1 ? 1u : 2u;
+    if (const char* env = getenv("RTB200_PRIMARY_KERNEL")) s->primary_kernel = atoi(env) == 1 ? 1u : 2u;
+    s->trace_chunks = opt.trace_chunks != 0;
     if (const char* env = getenv("RTB200_TRACE_CHUNKS")) s->trace_chunks = atoi(env) != 0;
-    s->cam_cell_px = 2.0f;
+    s->cam_cell_px = opt.cam_cell_px > 0.0f ? opt.cam_cell_px : 2.0f;
     if (const char* env = getenv("RTB200_CAM_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->cam_cell_px = v; }
+    s->primary_mode = opt.primary_mode == 1 ? 1 : 0;
     if (const char* env = getenv("RTB200_PRIMARY")) s->primary_mode = strcmp(env, "bvh") == 0 ? 1 : 0;
+    TRY_(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    TRY_(cudaEventCreateWithFlags(&s->ev_prefix, cudaEventDisableTiming));
+    TRY_(cudaEventCreateWithFlags(&s->ev_samples, cudaEventDisableTiming));
+    TRY_(cudaEventCreateWithFlags(&s->ev_idle, cudaEventDisableTiming));
     if (const char* env = getenv("RTB200_GRID_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->grid_cell_factor = v; }
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
@@ -227,9 +274,12 @@ int rtb_scene_create(const rtb_scene_desc* desc, rtb_scene** out) {
         TRY_(cudaMalloc(&s->d_tris, (size_t)n * 3 * sizeof(float4)));
         TRY_(cudaMalloc(&s->d_colors4, (size_t)n * sizeof(float4)));
         TRY_(rtb_build_scene(d_verts, d_colors, d_rank, n, s->d_tris, s->d_colors4, &s->d_nodes, &s->root, &s->info, s->stream));
+        s->tie_mode = desc->tie_rank ? RTB_TIE_CALLER : RTB_TIE_INDEX;
         if (!desc->tie_rank && n > 1 && n <= RTB_TIE_RANK_MAX_TRIS) {
             TRY_(rtb_tie_rank_device(s->d_tris, n, nullptr, s->d_colors4, s->stream));
+            s->tie_mode = RTB_TIE_REFERENCE;
         }
+        if (!desc->tie_rank && n <= 1) s->tie_mode = RTB_TIE_REFERENCE;
         TRY_(cudaStreamSynchronize(s->stream));
         TRY_(rtb_grid_scene_stats(s->grid, s->d_tris, n, s->stream));
         if (s->info.max_depth > RTB_STACK_SIZE - 1) {
@@ -259,6 +309,7 @@ int rtb_scene_get_info(const rtb_scene* s, rtb_scene_info* info) {
     if (!s || !info) return fail(RTB_ERR_ARG, "rtb_scene_get_info: null argument");
     info->n_tris = s->n_tris; info->n_nodes = s->info.n_nodes; info->max_depth = s->info.max_depth;
     info->ploc_iterations = s->info.iterations; info->sah_cost = s->info.sah_cost; info->build_ms = s->info.build_ms;
+    info->tie_mode = s->tie_mode;
     return RTB_OK;
 }
 
@@ -270,8 +321,38 @@ int rtb_scene_set_samples(rtb_scene* s, const float* samples, uint32_t n_pairs) 
         CUDA_TRY(cudaMalloc(&s->d_samples, (size_t)n_pairs * sizeof(float2)));
         s->n_samples = n_pairs;
     }
+    s->samples_pending = false;
     CUDA_TRY(cudaMemcpyAsync(s->d_samples, samples, (size_t)n_pairs * sizeof(float2), cudaMemcpyHostToDevice, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->samples_version++;
+    return RTB_OK;
+}
+
+#define RTB_SAMPLES_PREFIX 65536u      // pairs uploaded first (512 KB): far more than any frame's light points (nb_ray^2 + nb_light_sample)
+
+int rtb_scene_set_samples_async(rtb_scene* s, const float* samples, uint32_t n_pairs) {
+    if (!s || !samples || n_pairs == 0) return fail(RTB_ERR_ARG, "rtb_scene_set_samples_async: null/empty table");
+    cudaPointerAttributes pa;
+    const bool pinned = cudaPointerGetAttributes(&pa, samples) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    if (!pinned) { cudaGetLastError(); return rtb_scene_set_samples(s, samples, n_pairs); }
+    CUDA_TRY(cudaSetDevice(s->device));
+    if (n_pairs != s->n_samples) {
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+        cudaFree(s->d_samples); s->d_samples = nullptr; s->n_samples = 0;
+        CUDA_TRY(cudaMalloc(&s->d_samples, (size_t)n_pairs * sizeof(float2)));
+        s->n_samples = n_pairs;
+    }
+    // the previous frame (on the scene's stream) has read the old table: the copy stream starts after it
+    CUDA_TRY(cudaEventRecord(s->ev_idle, s->stream));
+    CUDA_TRY(cudaStreamWaitEvent(s->copy_stream, s->ev_idle, 0));
+    const uint32_t prefix = n_pairs < RTB_SAMPLES_PREFIX ? n_pairs : RTB_SAMPLES_PREFIX;
+    CUDA_TRY(cudaMemcpyAsync(s->d_samples, samples, (size_t)prefix * sizeof(float2), cudaMemcpyHostToDevice, s->stream));
+    CUDA_TRY(cudaEventRecord(s->ev_prefix, s->stream));
+    if (n_pairs > prefix)
+        CUDA_TRY(cudaMemcpyAsync(s->d_samples + prefix, samples + 2 * (size_t)prefix, (size_t)(n_pairs - prefix) * sizeof(float2),
+                                 cudaMemcpyHostToDevice, s->copy_stream));
+    CUDA_TRY(cudaEventRecord(s->ev_samples, s->copy_stream));
+    s->samples_pending = true; s->samples_prefix = prefix;
     s->samples_version++;
     return RTB_OK;
 }
@@ -279,7 +360,7 @@ int rtb_scene_set_samples(rtb_scene* s, const float* samples, uint32_t n_pairs) 
 }  // extern "C"
 
 // Validates params, (re)builds the light-point table on `st`, fills TraceArgs.
-static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t st, TraceArgs* a) {
+static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t st, TraceArgs* a, bool allow_spec = false) {
     if (!s || !p) return fail(RTB_ERR_ARG, "render: null argument");
     if (!s->d_samples) return fail(RTB_ERR_STATE, "render: rtb_scene_set_samples has not been called");
     if (p->width == 0 || p->height == 0) return fail(RTB_ERR_ARG, "render: empty frame");
@@ -299,6 +380,11 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     const bool lights_cached = s->light_key_set && s->light_key_samples == s->samples_version && s->light_key_need == need &&
                                s->light_key_nb_ray == p->nb_ray && s->light_key_nls == p->nb_light_sample && s->light_key_stream == st;
     s->light_tables_ran = !lights_cached;
+    s->grid_rebuilds = 0;
+    if (s->samples_pending) {                     // asynchronous table upload: the light tables need its prefix only
+        if (st != s->stream) CUDA_TRY(cudaStreamWaitEvent(st, s->ev_prefix, 0));
+        if (need > s->samples_prefix) CUDA_TRY(cudaStreamWaitEvent(st, s->ev_samples, 0));
+    }
     if (!lights_cached) CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
     // light-sample groups (k_light_groups): at most RTB_MAX_GROUPS runs of the Hilbert-sorted samples, ~32 samples each
 #ifndef RTB_GROUP_TARGET
@@ -331,7 +417,8 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     // light grids: one per light point the frame addresses; cached until the table or that count changes
     if (s->shadow_mode != 1 && p->nb_ray && p->nb_light_sample &&
         !(s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need)) {
-        CUDA_TRY(rtb_grid_build(s->grid, s->d_tris, s->n_tris, s->d_light_pts, (uint32_t)need, s->grid_cell_factor, st));
+        CUDA_TRY(rtb_grid_build(s->grid, s->d_tris, s->n_tris, s->d_light_pts, (uint32_t)need, s->grid_cell_factor, allow_spec, st));
+        s->grid_rebuilds++;
         s->grid.key_set = true; s->grid.key_samples = s->samples_version; s->grid.key_n_lights = (uint32_t)need;
     }
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
@@ -344,6 +431,7 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         a->grid_big = s->grid.d_big; a->grid_n_big = s->grid.n_big;
         a->grid_union = s->grid.d_union; a->grid_sat = s->grid.d_sat;
     }
+    a->shadow_kernel = s->shadow_kernel; a->primary_kernel = s->primary_kernel;
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
     a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;
     a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;
@@ -354,7 +442,8 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         if (!(s->cam_key_set && memcmp(&s->cam_key, &a->cam, sizeof(CameraBasis)) == 0)) {
             if (!s->d_cam_tris) CUDA_TRY(cudaMalloc(&s->d_cam_tris, (size_t)s->n_tris * 3 * sizeof(float4)));
             if (!s->d_cam_origin) CUDA_TRY(cudaMalloc(&s->d_cam_origin, sizeof(float4)));
-            CUDA_TRY(rtb_cam_grid_build(s->cam_grid, s->d_tris, s->n_tris, s->d_cam_tris, s->d_cam_origin, a->cam, s->cam_cell_px, st));
+            CUDA_TRY(rtb_cam_grid_build(s->cam_grid, s->d_tris, s->n_tris, s->d_cam_tris, s->d_cam_origin, a->cam, s->cam_cell_px, allow_spec, st));
+            s->grid_rebuilds++;
             s->cam_key = a->cam; s->cam_key_set = true;
         }
         if (s->cam_grid.valid) {
@@ -374,7 +463,47 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         a->cdiv_bad = s->d_cdiv_bad;
     }
     a->counters = s->d_counters;
+    if (s->samples_pending) CUDA_TRY(cudaStreamWaitEvent(st, s->ev_samples, 0));     // the primary-ray kernel reads the whole table
     return RTB_OK;
+}
+
+// After the caller has synchronised: the verdict of speculative grid builds enqueued by prepare_args(allow_spec).  *redo: at
+// least one did not fit its allocation -- its grids were switched off on the device, the frame is wrong; the cache keys are
+// dropped so that the next prepare_args builds synchronously (with room) and the caller renders again.
+static int validate_grids(rtb_scene* s, bool* redo) {
+    *redo = false;
+    bool ok = true;
+    CUDA_TRY(rtb_grid_validate(s->grid, s->stream, &ok));
+    if (!ok) { s->grid.key_set = false; *redo = true; }
+    CUDA_TRY(rtb_grid_validate(s->cam_grid, s->stream, &ok));
+    if (!ok) { s->cam_key_set = false; *redo = true; }
+    return RTB_OK;
+}
+
+// Copies local rows [r0, r1) of a rank's compact device rows to the host.  frame_rows: h is the FULL frame and every band goes
+// to its own rows (band lb of this rank = frame band lb * world + rank): whole bands as one strided 2-D copy.
+static cudaError_t copy_rows_to_host(uint8_t* h, const uint8_t* d, uint64_t r0, uint64_t r1, const TraceArgs& a, bool frame_rows, cudaStream_t st) {
+    const size_t rb = (size_t)a.width * 3;
+    if (r1 <= r0) return cudaSuccess;
+    if (!frame_rows || a.world <= 1) return cudaMemcpyAsync(h + r0 * rb, d + r0 * rb, (r1 - r0) * rb, cudaMemcpyDeviceToHost, st);
+    const uint64_t B = a.band_rows;
+    uint64_t lr = r0;
+    while (lr < r1) {
+        const uint64_t lb = lr / B, within = lr - lb * B;
+        const uint64_t grow = (lb * a.world + a.rank) * B + within;          // frame row of local row lr
+        cudaError_t e;
+        if (within == 0 && r1 - lr >= B) {
+            const uint64_t nb = (r1 - lr) / B;
+            e = cudaMemcpy2DAsync(h + grow * rb, (size_t)a.world * B * rb, d + lr * rb, B * rb, B * rb, nb, cudaMemcpyDeviceToHost, st);
+            lr += nb * B;
+        } else {
+            const uint64_t n = (B - within) < (r1 - lr) ? (B - within) : (r1 - lr);
+            e = cudaMemcpyAsync(h + grow * rb, d + lr * rb, n * rb, cudaMemcpyDeviceToHost, st);
+            lr += n;
+        }
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
 }
 
 #define RTB_MAX_TIMED_CHUNKS 32
@@ -435,7 +564,7 @@ static int reserve_wavefront(rtb_scene::WaveBufs& b, uint64_t rays, uint32_t n_g
 // list, in chunks of at most s->chunk_rays rays so that the intermediate buffers stay bounded (about 170 bytes per ray
 // in the worst case) whatever the resolution and rays per pixel.  A chunk is a whole number of tile rows (or of 256
 // listed pixels).  timed: record the per-kernel events of the first RTB_MAX_TIMED_CHUNKS chunks.
-static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st, bool timed, uint8_t* h_rows = nullptr) {
+static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st, bool timed, uint8_t* h_rows = nullptr, bool h_frame_rows = false) {
     s->timed_chunks = 0; s->n_chunks = 0; s->terms_ran = false;
     uint64_t unit, units_total;                       // pixels per granule, granules
     if (a.pixel_list) {
@@ -502,8 +631,7 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
             // pinned host frame (rtb_render): the rows of this chunk leave right behind its k_shade, on the chunk's own stream,
             // so the device-to-host copy of one chunk overlaps the kernels of the next
             const uint64_t r0 = u0 * 4 < a.owned_rows ? u0 * 4 : a.owned_rows, r1 = (u0 + nu) * 4 < a.owned_rows ? (u0 + nu) * 4 : a.owned_rows;
-            const size_t off = (size_t)r0 * a.width * 3, bytes = (size_t)(r1 - r0) * a.width * 3;
-            if (bytes) CUDA_TRY(cudaMemcpyAsync(h_rows + off, a.rgb8 + off, bytes, cudaMemcpyDeviceToHost, cs));
+            CUDA_TRY(copy_rows_to_host(h_rows, a.rgb8, r0, r1, a, h_frame_rows, cs));
         }
         s->n_chunks++;
     }
@@ -542,6 +670,7 @@ static int fetch_stats(rtb_scene* s, const rtb_render_params* p, uint64_t n_pix,
         st->primary_ms = k_ms[0]; st->shadow_ms = k_ms[1]; st->shade_ms = k_ms[2];
         st->queued_hits = (uint32_t)h[RTB_CTR_QUEUED]; st->queued_groups = (uint32_t)h[RTB_CTR_PAIRS];
         st->queued_walks = (uint32_t)h[RTB_CTR_WALKS];
+        st->grid_rebuilds = s->grid_rebuilds; st->grid_redo = s->grid_redo;
     }
     return RTB_OK;
 }
@@ -591,31 +720,80 @@ int rtb_peer_close(int32_t device, void* d_ptr, int32_t owner) {
     return RTB_OK;
 }
 
-int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stats* stats) {
-    TraceArgs a;
-    if (!rgb8) return fail(RTB_ERR_ARG, "rtb_render: null output");
-    int rc = prepare_args(s, p, s ? s->stream : nullptr, &a);
-    if (rc != RTB_OK) return rc;
-    const size_t bytes = (size_t)a.owned_rows * a.width * 3;
-    if (bytes > s->frame_cap) {
-        cudaFree(s->d_frame); s->d_frame = nullptr; s->frame_cap = 0;
-        CUDA_TRY(cudaMalloc(&s->d_frame, bytes));
-        s->frame_cap = bytes;
+// render(): the frame (or this rank's bands) into HOST memory.  h_rgb8: compact rows, or the full frame with RTB_FLAG_FRAME_ROWS.
+// d_full != nullptr (rtb_render_multi with RTB_FLAG_GATHER_PEER): the rows go to their place in that device frame (possibly a
+// peer's) instead and nothing is copied to the host here.
+// The light grids / camera grid a new table / camera needs are rebuilt speculatively (rtb_grid.cu: no host synchronisation
+// between the build's passes and the frame's kernels); after the frame's one synchronisation the builds are validated and, should
+// one not have fitted its allocation, rebuilt synchronously and the frame rendered once more.
+static int render_core(rtb_scene* s, const rtb_render_params* p, uint8_t* h_rgb8, uint8_t* d_full, rtb_stats* stats) {
+    if (!s || !p) return fail(RTB_ERR_ARG, "render: null argument");
+    s->grid_redo = 0;
+    uint32_t rebuilds = 0;
+    for (int attempt = 0; ; ++attempt) {
+        TraceArgs a;
+        int rc = prepare_args(s, p, s->stream, &a, attempt == 0 && !getenv("RTB200_NO_SPEC"));
+        if (rc != RTB_OK) return rc;
+        rebuilds += s->grid_rebuilds;
+        const size_t bytes = (size_t)a.owned_rows * a.width * 3;
+        const bool h_frame_rows = !d_full && (p->flags & RTB_FLAG_FRAME_ROWS) != 0 && a.world > 1;
+        if (!d_full && bytes > s->frame_cap) {
+            cudaFree(s->d_frame); s->d_frame = nullptr; s->frame_cap = 0;
+            CUDA_TRY(cudaMalloc(&s->d_frame, bytes));
+            s->frame_cap = bytes;
+        }
+        a.rgb8 = d_full ? d_full : s->d_frame;
+        a.frame_rows = d_full ? 1u : 0u;
+        CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
+        // a pinned destination takes per-chunk copies (an asynchronous copy to pageable memory would block the host chunk by chunk)
+        bool pinned = false;
+        if (h_rgb8) {
+            cudaPointerAttributes pa;
+            pinned = cudaPointerGetAttributes(&pa, h_rgb8) == cudaSuccess && pa.type == cudaMemoryTypeHost && !(p->flags & RTB_FLAG_PROFILE);
+            if (!pinned) cudaGetLastError();
+        }
+        rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0, pinned ? h_rgb8 : nullptr, h_frame_rows);
+        if (rc != RTB_OK) return rc;
+        CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
+        uint8_t* stage = nullptr;
+        if (h_rgb8 && bytes && !pinned) {
+            if (h_frame_rows) {                    // pageable full frame: compact rows through the scene's pinned buffer, placed by the host below
+                if (bytes > s->pinned_cap) {
+                    if (s->h_pinned) cudaFreeHost(s->h_pinned);
+                    s->h_pinned = nullptr; s->pinned_cap = 0;
+                    CUDA_TRY(cudaMallocHost(&s->h_pinned, bytes));
+                    s->pinned_cap = bytes;
+                }
+                stage = s->h_pinned;
+                CUDA_TRY(cudaMemcpyAsync(stage, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
+            } else {
+                CUDA_TRY(cudaMemcpyAsync(h_rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
+            }
+        }
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
+        s->samples_pending = false;
+        bool redo = false;
+        rc = validate_grids(s, &redo);
+        if (rc != RTB_OK) return rc;
+        if (redo && attempt == 0) { s->grid_redo++; continue; }
+        if (redo) return fail(RTB_ERR_STATE, "render: grid rebuild failed twice");
+        if (stage) {
+            const size_t rb = (size_t)a.width * 3;
+            for (uint32_t lr = 0; lr < a.owned_rows; ++lr) {
+                const uint32_t lb = lr / a.band_rows, within = lr - lb * a.band_rows;
+                memcpy(h_rgb8 + (size_t)((lb * a.world + a.rank) * a.band_rows + within) * rb, stage + (size_t)lr * rb, rb);
+            }
+        }
+        float ms = 0.0f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        s->grid_rebuilds = rebuilds;
+        return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 8, stats);
     }
-    a.rgb8 = s->d_frame;
-    CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
-    // a pinned destination takes per-chunk copies (an asynchronous copy to pageable memory would block the host chunk by chunk)
-    cudaPointerAttributes pa;
-    const bool pinned = cudaPointerGetAttributes(&pa, rgb8) == cudaSuccess && pa.type == cudaMemoryTypeHost && !(p->flags & RTB_FLAG_PROFILE);
-    if (!pinned) cudaGetLastError();
-    rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0, pinned ? rgb8 : nullptr);
-    if (rc != RTB_OK) return rc;
-    CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
-    if (bytes && !pinned) CUDA_TRY(cudaMemcpyAsync(rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
-    CUDA_TRY(cudaStreamSynchronize(s->stream));
-    float ms = 0.0f;
-    CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-    return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 8, stats);
+}
+
+int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stats* stats) {
+    if (!rgb8) return fail(RTB_ERR_ARG, "rtb_render: null output");
+    return render_core(s, p, rgb8, nullptr, stats);
 }
 
 int rtb_render_pixels(rtb_scene* s, const rtb_render_params* p, const uint32_t* pixels, uint64_t n_pix, float* rgb_lin,
@@ -732,3 +910,359 @@ int rtb_deinterleave_bands(int32_t device, const void* d_staged, uint64_t stride
 }
 
 }  // extern "C"
+
+// ---- several GPUs behind one call ---------------------------------------------------------------------------------------------
+// One host thread per device (the reference's render() fans out to its own worker threads and joins them, src/main.rs:269-303).
+struct MultiJob { int rc; std::string err; rtb_stats st; };
+
+template <typename F>
+static int run_per_device(uint32_t n, F&& fn, std::vector<MultiJob>& jobs) {
+    jobs.assign(n, MultiJob());
+    std::vector<std::thread> th;
+    auto body = [&](uint32_t i) {
+        memset(&jobs[i].st, 0, sizeof(rtb_stats));
+        jobs[i].rc = fn(i, &jobs[i].st);
+        if (jobs[i].rc != RTB_OK) jobs[i].err = g_err;
+    };
+    for (uint32_t i = 1; i < n; ++i) th.emplace_back(body, i);
+    body(0);
+    for (auto& t : th) t.join();
+    for (uint32_t i = 0; i < n; ++i)
+        if (jobs[i].rc != RTB_OK) return fail(jobs[i].rc, "device %u: %s", i, jobs[i].err.c_str());
+    return RTB_OK;
+}
+
+extern "C" int rtb_scenes_set_samples(rtb_scene* const* scenes, uint32_t n_gpus, const float* samples, uint32_t n_pairs) {
+    if (!scenes || n_gpus == 0) return fail(RTB_ERR_ARG, "rtb_scenes_set_samples: no scenes");
+    for (uint32_t i = 0; i < n_gpus; ++i) if (!scenes[i]) return fail(RTB_ERR_ARG, "rtb_scenes_set_samples: scene %u is null", i);
+    std::vector<MultiJob> jobs;
+    return run_per_device(n_gpus, [&](uint32_t i, rtb_stats*) { return rtb_scene_set_samples_async(scenes[i], samples, n_pairs); }, jobs);
+}
+
+extern "C" int rtb_render_multi(rtb_scene* const* scenes, uint32_t n_gpus, const rtb_render_params* params, uint8_t* rgb8, rtb_stats* stats) {
+    if (!scenes || n_gpus == 0 || !params || !rgb8) return fail(RTB_ERR_ARG, "rtb_render_multi: null argument");
+    for (uint32_t i = 0; i < n_gpus; ++i) {
+        if (!scenes[i]) return fail(RTB_ERR_ARG, "rtb_render_multi: scene %u is null", i);
+        for (uint32_t j = 0; j < i; ++j)
+            if (scenes[j]->device == scenes[i]->device) return fail(RTB_ERR_ARG, "rtb_render_multi: scenes %u and %u share device %d", j, i, scenes[i]->device);
+    }
+    rtb_render_params base = *params;
+    if (base.band_rows == 0) base.band_rows = 4;
+    base.world = n_gpus;
+    base.flags = (params->flags & ~(RTB_FLAG_GATHER_PEER)) | RTB_FLAG_FRAME_ROWS;
+    const bool peer = (params->flags & RTB_FLAG_GATHER_PEER) != 0 && n_gpus > 1;
+    const size_t frame_bytes = (size_t)params->width * params->height * 3;
+    uint8_t* d_full = nullptr;
+    if (peer) {
+        rtb_scene* s0 = scenes[0];
+        CUDA_TRY(cudaSetDevice(s0->device));
+        if (frame_bytes > s0->full_cap) {
+            cudaFree(s0->d_full); s0->d_full = nullptr; s0->full_cap = 0;
+            CUDA_TRY(cudaMalloc(&s0->d_full, frame_bytes));
+            s0->full_cap = frame_bytes;
+        }
+        d_full = s0->d_full;
+        for (uint32_t i = 1; i < n_gpus; ++i) {          // NVLink peer stores from device i into device 0's frame
+            int can = 0;
+            CUDA_TRY(cudaDeviceCanAccessPeer(&can, scenes[i]->device, s0->device));
+            if (!can) return fail(RTB_ERR_CUDA, "rtb_render_multi: device %d cannot access device %d (no peer path)", scenes[i]->device, s0->device);
+            CUDA_TRY(cudaSetDevice(scenes[i]->device));
+            const cudaError_t e = cudaDeviceEnablePeerAccess(s0->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return fail(RTB_ERR_CUDA, "cudaDeviceEnablePeerAccess: %s", cudaGetErrorString(e));
+            cudaGetLastError();
+        }
+    }
+    std::vector<MultiJob> jobs;
+    int rc = run_per_device(n_gpus, [&](uint32_t i, rtb_stats* st) {
+        rtb_render_params p = base;
+        p.rank = i;
+        return render_core(scenes[i], &p, peer ? nullptr : rgb8, d_full, st);
+    }, jobs);
+    if (rc != RTB_OK) return rc;
+    if (peer) {                                          // every device has synchronised its stream: the frame is complete
+        CUDA_TRY(cudaSetDevice(scenes[0]->device));
+        CUDA_TRY(cudaMemcpyAsync(rgb8, d_full, frame_bytes, cudaMemcpyDeviceToHost, scenes[0]->stream));
+        CUDA_TRY(cudaStreamSynchronize(scenes[0]->stream));
+    }
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        for (uint32_t i = 0; i < n_gpus; ++i) {
+            const rtb_stats& t = jobs[i].st;
+            stats->primary_rays += t.primary_rays; stats->primary_hits += t.primary_hits; stats->shadow_rays += t.shadow_rays;
+            stats->shadow_occluded += t.shadow_occluded; stats->box_tests += t.box_tests; stats->tri_tests += t.tri_tests;
+            stats->launches += t.launches; stats->queued_hits += t.queued_hits; stats->queued_groups += t.queued_groups;
+            stats->queued_walks += t.queued_walks; stats->grid_rebuilds += t.grid_rebuilds; stats->grid_redo += t.grid_redo;
+            if (t.kernel_ms > stats->kernel_ms) stats->kernel_ms = t.kernel_ms;
+            if (t.primary_ms > stats->primary_ms) stats->primary_ms = t.primary_ms;
+            if (t.shadow_ms > stats->shadow_ms) stats->shadow_ms = t.shadow_ms;
+            if (t.shade_ms > stats->shade_ms) stats->shade_ms = t.shade_ms;
+            if (t.grid_build_ms > stats->grid_build_ms) stats->grid_build_ms = t.grid_build_ms;
+            stats->grid_cells = t.grid_cells; stats->grid_entries = t.grid_entries; stats->grid_big = t.grid_big;
+        }
+    }
+    return RTB_OK;
+}
+
+// ---- frame sequences ----------------------------------------------------------------------------------------------
+// A pool of host threads that encodes finished frames to PNG while the GPU renders the next ones (img.save, src/main.rs:312-315).
+struct PngPool {
+    std::mutex m; std::condition_variable cv_put, cv_get;
+    std::deque<std::pair<std::string, std::vector<uint8_t>>> q;
+    std::vector<std::thread> th;
+    uint32_t w = 0, h = 0; bool done = false; int rc = RTB_OK; std::string err;
+    void start(uint32_t width, uint32_t rows, unsigned n) {
+        w = width; h = rows;
+        for (unsigned i = 0; i < n; ++i) th.emplace_back([this] {
+            for (;;) {
+                std::pair<std::string, std::vector<uint8_t>> job;
+                {
+                    std::unique_lock<std::mutex> lk(m);
+                    cv_get.wait(lk, [this] { return done || !q.empty(); });
+                    if (q.empty()) return;
+                    job = std::move(q.front()); q.pop_front();
+                    cv_put.notify_one();
+                }
+                const int r = rtb_write_png(job.first.c_str(), job.second.data(), w, h);
+                if (r != RTB_OK) { std::lock_guard<std::mutex> lk(m); if (rc == RTB_OK) { rc = r; err = rtb_last_error(); } }
+            }
+        });
+    }
+    void put(const std::string& path, const uint8_t* rgb8) {
+        std::vector<uint8_t> copy(rgb8, rgb8 + (size_t)w * h * 3);
+        std::unique_lock<std::mutex> lk(m);
+        cv_put.wait(lk, [this] { return q.size() < 2 * th.size() + 2; });          // bounded: at most a few frames of memory
+        q.emplace_back(path, std::move(copy));
+        cv_get.notify_one();
+    }
+    void finish() {
+        { std::lock_guard<std::mutex> lk(m); done = true; }
+        cv_get.notify_all();
+        for (auto& t : th) t.join();
+        th.clear();
+    }
+};
+
+// Poses first, first + stride, ... of `poses` on one scene.  Frame k goes to d_seq[k & 1] -> h_seq[k & 1] (pinned); a consumer
+// thread delivers it when its copy has landed, while the submitting thread is already enqueueing frame k + 1.  The camera grid of
+// every pose is a speculative rebuild; its control words are snapshotted behind the frame's kernels and checked by the consumer.
+static int sequence_on_scene(rtb_scene* s, const rtb_render_params* params, const rtb_camera_pose* poses, uint32_t n_poses, uint32_t first,
+                             uint32_t stride, uint8_t* frames, const char* png_pattern, PngPool* pool, rtb_frame_fn on_frame, void* user,
+                             rtb_sequence_stats* stats) {
+    if (!s || !params || (!poses && n_poses)) return fail(RTB_ERR_ARG, "rtb_render_sequence: null argument");
+    CUDA_TRY(cudaSetDevice(s->device));
+    const uint32_t world = params->world ? params->world : 1;
+    const uint32_t rows = rtb_owned_rows(params->height, world > 1 ? params->band_rows : params->height, world > 1 ? params->rank : 0, world);
+    const size_t bytes = (size_t)rows * params->width * 3;
+    if (bytes > s->seq_cap) {
+        for (int k = 0; k < 2; ++k) { cudaFree(s->d_seq[k]); s->d_seq[k] = nullptr; if (s->h_seq[k]) cudaFreeHost(s->h_seq[k]); s->h_seq[k] = nullptr; }
+        s->seq_cap = 0;
+        for (int k = 0; k < 2; ++k) { CUDA_TRY(cudaMalloc(&s->d_seq[k], bytes ? bytes : 1)); CUDA_TRY(cudaMallocHost(&s->h_seq[k], bytes ? bytes : 1)); }
+        s->seq_cap = bytes;
+    }
+    if (!s->h_seq_ctl) CUDA_TRY(cudaMallocHost(&s->h_seq_ctl, 2 * 8 * sizeof(uint32_t)));
+    for (int k = 0; k < 2; ++k) if (!s->ev_seq[k]) CUDA_TRY(cudaEventCreateWithFlags(&s->ev_seq[k], cudaEventDisableTiming));
+    if (!s->ev_seq0) { CUDA_TRY(cudaEventCreate(&s->ev_seq0)); CUDA_TRY(cudaEventCreate(&s->ev_seq1)); }
+
+    // a pinned `frames` array takes the device-to-host copies directly (no staging frame, nothing for the consumer to copy)
+    bool direct = false;
+    if (frames && bytes) {
+        cudaPointerAttributes pa;
+        direct = cudaPointerGetAttributes(&pa, frames) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+        if (!direct) cudaGetLastError();
+    }
+    std::vector<uint32_t> mine;
+    for (uint32_t k = first; k < n_poses; k += stride) mine.push_back(k);
+    const uint32_t n = (uint32_t)mine.size();
+    const auto t_start = std::chrono::steady_clock::now();
+    // shared between the submitting thread (this one) and the consumer
+    std::mutex m; std::condition_variable cv;
+    uint32_t submitted = 0, consumed = 0;          // frames enqueued / delivered (local indices)
+    int64_t bad = -1;                               // local index of a frame whose camera grid did not fit: to be redone synchronously
+    bool fixed = false, abort_all = false;
+    int consumer_rc = RTB_OK; std::string consumer_err;
+    uint32_t redo_count = 0;
+    uint64_t primary_rays = 0;
+
+    std::thread consumer([&] {
+        cudaSetDevice(s->device);
+        for (uint32_t j = 0; j < n; ++j) {
+            {
+                std::unique_lock<std::mutex> lk(m);
+                cv.wait(lk, [&] { return submitted > j || abort_all; });
+                if (abort_all) return;
+            }
+            const int slot = (int)(j & 1);
+            cudaError_t e = cudaEventSynchronize(s->ev_seq[slot]);
+            if (e == cudaSuccess && s->h_seq_ctl[8 * slot + 4] != 0u) {           // the pose's camera grid was switched off: wrong frame
+                std::unique_lock<std::mutex> lk(m);
+                bad = j; fixed = false;
+                cv.notify_all();
+                cv.wait(lk, [&] { return fixed || abort_all; });
+                if (abort_all) return;
+                bad = -1;
+                e = cudaEventSynchronize(s->ev_seq[slot]);
+            }
+            if (e != cudaSuccess) {
+                std::lock_guard<std::mutex> lk(m);
+                consumer_rc = RTB_ERR_CUDA; consumer_err = cudaGetErrorString(e); abort_all = true; cv.notify_all();
+                return;
+            }
+            const uint32_t k = mine[j];
+            const uint8_t* h = direct ? frames + (size_t)k * bytes : s->h_seq[slot];
+            if (frames && !direct) memcpy(frames + (size_t)k * bytes, h, bytes);
+            if (png_pattern && pool) { char path[1024]; snprintf(path, sizeof(path), png_pattern, k); pool->put(path, h); }
+            if (on_frame) on_frame(user, k, h, params->width, rows);
+            { std::lock_guard<std::mutex> lk(m); consumed = j + 1; }
+            cv.notify_all();
+        }
+    });
+
+    int rc = RTB_OK;
+    auto submit = [&](uint32_t j, bool spec) -> int {
+        rtb_render_params p = *params;
+        const rtb_camera_pose& c = poses[mine[j]];
+        memcpy(p.eye, c.eye, sizeof(p.eye)); memcpy(p.look_at, c.look_at, sizeof(p.look_at)); memcpy(p.up, c.up, sizeof(p.up));
+        p.distance = c.distance;
+        TraceArgs a;
+        int r = prepare_args(s, &p, s->stream, &a, spec);
+        if (r != RTB_OK) return r;
+        const int slot = (int)(j & 1);
+        a.rgb8 = s->d_seq[slot]; a.frame_rows = 0;
+        r = run_wavefront(s, a, false, s->stream, false);
+        if (r != RTB_OK) return r;
+        primary_rays += (uint64_t)a.owned_rows * a.width * a.nb_ray;
+        if (bytes) CUDA_TRY(cudaMemcpyAsync(direct ? frames + (size_t)mine[j] * bytes : s->h_seq[slot], s->d_seq[slot], bytes, cudaMemcpyDeviceToHost, s->stream));
+        // snapshot of the camera grid's control words (failure bits) behind this frame: the next pose's build overwrites them
+        if (s->cam_grid.d_ctl && s->cam_grid.pending) CUDA_TRY(cudaMemcpyAsync(s->h_seq_ctl + 8 * slot, s->cam_grid.d_ctl, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+        else memset(s->h_seq_ctl + 8 * slot, 0, 8 * sizeof(uint32_t));
+        s->cam_grid.pending = false;
+        CUDA_TRY(cudaEventRecord(s->ev_seq[slot], s->stream));
+        return RTB_OK;
+    };
+
+    // the light grids (and a first camera grid) synchronously, once, before the pipeline starts
+    if (n) {
+        TraceArgs a0;
+        rtb_render_params p0 = *params;
+        const rtb_camera_pose& c0 = poses[mine[0]];
+        memcpy(p0.eye, c0.eye, sizeof(p0.eye)); memcpy(p0.look_at, c0.look_at, sizeof(p0.look_at)); memcpy(p0.up, c0.up, sizeof(p0.up)); p0.distance = c0.distance;
+        rc = prepare_args(s, &p0, s->stream, &a0, false);
+        if (rc == RTB_OK && cudaStreamSynchronize(s->stream) != cudaSuccess) rc = fail(RTB_ERR_CUDA, "rtb_render_sequence: stream error");
+        s->samples_pending = false;
+    }
+    if (rc == RTB_OK) cudaEventRecord(s->ev_seq0, s->stream);
+    const bool no_spec = getenv("RTB200_NO_SPEC") != nullptr;
+    for (uint32_t j = 0; j < n && rc == RTB_OK; ++j) {
+        {   // slot j & 1 is free once frame j - 2 has been delivered; a failed frame is repaired first
+            std::unique_lock<std::mutex> lk(m);
+            cv.wait(lk, [&] { return consumed + 2 > j || bad >= 0 || abort_all; });
+            if (abort_all) break;
+            if (bad >= 0) {
+                const uint32_t jb = (uint32_t)bad;
+                lk.unlock();
+                // everything in flight finishes; pose jb again with a synchronous camera-grid build (which also makes room), then on
+                if (cudaStreamSynchronize(s->stream) != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "rtb_render_sequence: stream error"); break; }
+                s->cam_key_set = false; s->cam_grid.spec_ok = false;
+                rc = submit(jb, false);
+                if (rc != RTB_OK) break;
+                redo_count++;
+                // frames after jb that were already enqueued used the old allocation as well: enqueue them again, in order
+                for (uint32_t j2 = jb + 1; j2 < j && rc == RTB_OK; ++j2) rc = submit(j2, !no_spec);
+                if (rc != RTB_OK) break;
+                lk.lock();
+                fixed = true; bad = -1;
+                cv.notify_all();
+                cv.wait(lk, [&] { return consumed + 2 > j || abort_all; });
+                if (abort_all) break;
+            }
+        }
+        rc = submit(j, !no_spec);
+        if (rc != RTB_OK) break;
+        { std::lock_guard<std::mutex> lk(m); submitted = j + 1; }
+        cv.notify_all();
+    }
+    // drain: the consumer may still report a bad frame among the last two
+    for (;;) {
+        std::unique_lock<std::mutex> lk(m);
+        if (rc != RTB_OK) { abort_all = true; cv.notify_all(); break; }
+        cv.wait(lk, [&] { return consumed >= n || bad >= 0 || abort_all; });
+        if (abort_all || consumed >= n) break;
+        const uint32_t jb = (uint32_t)bad;
+        lk.unlock();
+        if (cudaStreamSynchronize(s->stream) != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "rtb_render_sequence: stream error"); continue; }
+        s->cam_key_set = false; s->cam_grid.spec_ok = false;
+        rc = submit(jb, false);
+        redo_count++;
+        for (uint32_t j2 = jb + 1; j2 < n && rc == RTB_OK; ++j2) rc = submit(j2, !no_spec);
+        lk.lock();
+        if (rc == RTB_OK) { fixed = true; bad = -1; cv.notify_all(); }
+    }
+    consumer.join();
+    if (rc == RTB_OK && consumer_rc != RTB_OK) rc = fail(consumer_rc, "rtb_render_sequence: %s", consumer_err.c_str());
+    cudaEventRecord(s->ev_seq1, s->stream);
+    cudaStreamSynchronize(s->stream);
+    s->cam_grid.pending = false;
+    if (stats) {
+        float ms = 0.0f;
+        if (cudaEventElapsedTime(&ms, s->ev_seq0, s->ev_seq1) != cudaSuccess) { ms = 0.0f; cudaGetLastError(); }
+        stats->device_ms = ms;
+        stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count();
+        stats->frames = consumed; stats->cam_grid_redo = redo_count; stats->primary_rays = primary_rays; stats->shadow_rays = 0;
+    }
+    return rc;
+}
+
+extern "C" int rtb_render_sequence(rtb_scene* scene, const rtb_render_params* params, const rtb_camera_pose* poses, uint32_t n_poses,
+                        uint8_t* frames, const char* png_pattern, rtb_frame_fn on_frame, void* user, rtb_sequence_stats* stats) {
+    if (!scene || !params) return fail(RTB_ERR_ARG, "rtb_render_sequence: null argument");
+    PngPool pool;
+    if (png_pattern) {
+        const uint32_t world = params->world ? params->world : 1;
+        const uint32_t rows = rtb_owned_rows(params->height, world > 1 ? params->band_rows : params->height, world > 1 ? params->rank : 0, world);
+        unsigned nt = std::thread::hardware_concurrency(); nt = nt > 8 ? 8 : (nt < 2 ? 2 : nt);
+        pool.start(params->width, rows, nt);
+    }
+    if (stats) memset(stats, 0, sizeof(*stats));
+    int rc = sequence_on_scene(scene, params, poses, n_poses, 0, 1, frames, png_pattern, png_pattern ? &pool : nullptr, on_frame, user, stats);
+    if (png_pattern) {
+        pool.finish();
+        if (rc == RTB_OK && pool.rc != RTB_OK) rc = fail(pool.rc, "rtb_render_sequence: %s", pool.err.c_str());
+        if (stats) stats->seconds += 0.0;
+    }
+    return rc;
+}
+
+extern "C" int rtb_render_sequence_multi(rtb_scene* const* scenes, uint32_t n_gpus, const rtb_render_params* params, const rtb_camera_pose* poses,
+                              uint32_t n_poses, uint8_t* frames, const char* png_pattern, rtb_sequence_stats* stats) {
+    if (!scenes || n_gpus == 0 || !params) return fail(RTB_ERR_ARG, "rtb_render_sequence_multi: null argument");
+    for (uint32_t i = 0; i < n_gpus; ++i) if (!scenes[i]) return fail(RTB_ERR_ARG, "rtb_render_sequence_multi: scene %u is null", i);
+    rtb_render_params p = *params;
+    p.world = 1; p.rank = 0;                              // whole frames, frame-parallel
+    PngPool pool;
+    if (png_pattern) {
+        unsigned nt = std::thread::hardware_concurrency(); nt = nt > 16 ? 16 : (nt < 2 ? 2 : nt);
+        pool.start(p.width, p.height, nt);
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<rtb_sequence_stats> st(n_gpus);
+    std::vector<MultiJob> jobs;
+    int rc = run_per_device(n_gpus, [&](uint32_t i, rtb_stats*) {
+        memset(&st[i], 0, sizeof(st[i]));
+        return sequence_on_scene(scenes[i], &p, poses, n_poses, i, n_gpus, frames, png_pattern, png_pattern ? &pool : nullptr, nullptr, nullptr, &st[i]);
+    }, jobs);
+    if (png_pattern) {
+        pool.finish();
+        if (rc == RTB_OK && pool.rc != RTB_OK) rc = fail(pool.rc, "rtb_render_sequence_multi: %s", pool.err.c_str());
+    }
+    if (stats) {
+        memset(stats, 0, sizeof(*stats));
+        for (uint32_t i = 0; i < n_gpus; ++i) {
+            stats->frames += st[i].frames; stats->cam_grid_redo += st[i].cam_grid_redo; stats->primary_rays += st[i].primary_rays;
+            if (st[i].device_ms > stats->device_ms) stats->device_ms = st[i].device_ms;
+        }
+        stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return rc;
+}
+
+

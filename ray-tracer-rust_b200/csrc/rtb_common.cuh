@@ -70,10 +70,21 @@ struct GridArgs {                  // build-time arguments
     uint32_t* cell_fill;           // per cell count / cursor
     int* entries;
     int* big_list;
-    uint32_t* ctl;                 // [0] total cells [1] big primitives [2] union nx [3] union nz
+    uint32_t* ctl;                 // [0] total cells [1] big primitives [2] union nx [3] union nz [4] failure bits (RTB_GRID_FAIL_*)
+                                   // [6,7] total entries as one 64-bit count (a 32-bit scan of the per-cell counts can wrap)
     GridUnion* uni; uint32_t* sat; // union occupancy: (nz + 1) x (nx + 1) summed-area table with a zero border
     uint32_t cell_cap;
+    // speculative rebuild (no host synchronisation): the arrays keep the capacity of the previous build and the kernels check
+    // themselves against it; a grid that does not fit is disabled on the device (every nx = 0) and the failure is reported in ctl[4]
+    uint32_t speculative;          // 1: check against the *_alloc capacities below instead of reporting sizes to the host
+    uint32_t cells_alloc;          // cell_start / cell_fill entries allocated (total cells + 1 must fit)
+    uint32_t expect_big;           // big-list length the caller's kernel arguments assume
+    uint64_t sat_alloc, entries_alloc;
 };
+#define RTB_GRID_FAIL_CELLS 1u     // more cells than allocated
+#define RTB_GRID_FAIL_BIG 2u       // big list longer than RTB_GRID_MAX_BIG or different from the expected length
+#define RTB_GRID_FAIL_SAT 4u       // union table larger than allocated
+#define RTB_GRID_FAIL_ENTRIES 8u   // more entries than allocated (or than a 32-bit offset can address)
 
 struct RtbGrid {                   // host-side owner of the light grids of one scene (rtb_grid.cu)
     float y_min, mean_extent; bool stats_ok;
@@ -84,6 +95,12 @@ struct RtbGrid {                   // host-side owner of the light grids of one 
     bool valid; uint32_t n_lights, n_big, total_cells, total_entries; float build_ms;
     // cache key: the grids depend on the sample table and on how many of its entries the frame addresses
     uint64_t key_samples; uint32_t key_n_lights; bool key_set;
+    // speculative rebuilds (rtb_grid.cu: grid_build_ex): state of the last synchronous build and of a pending speculative one
+    bool spec_ok; uint32_t spec_n_tris, spec_n_big_; float spec_cell0, spec_y_plane; bool spec_with_union;
+    bool pending;                  // a speculative build has been enqueued and not validated yet (rtb_grid_validate)
+    uint64_t entry_cap_limit;      // entries above which the grid path is not taken (0 = default 512 Mi); tests lower it
+    cudaEvent_t ev0, ev1;          // build time
+    uint32_t builds, spec_builds, spec_failures;   // statistics
 };
 
 // hit record / queue item words (rtb_trace.cu)
@@ -102,6 +119,7 @@ struct TraceArgs {
     const float2* __restrict__ samples;  // n_samples (u,v) pairs
     const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table
     uint32_t frame_rows;                    // 1: rgb8 is the full frame, owned rows go to their own position (RTB_FLAG_FRAME_ROWS)
+    uint32_t shadow_kernel, primary_kernel; // kernel forms (rtb_scene_options): 0 / 2 = current, 1 = the round-1 kernels
     const float4* __restrict__ light_pairs; // pair table of the same points (k_light_pairs), 2 float4 per point
     const float* __restrict__ light_box; // 6 floats: component-wise min / max of light_pts[0..n_light_pts)
     const uint16_t* __restrict__ light_perm; // [nb_ray][nb_light_sample] sample at sorted position j (k_light_groups), nullptr = identity

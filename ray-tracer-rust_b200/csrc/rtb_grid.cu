@@ -166,15 +166,45 @@ __global__ void __launch_bounds__(1024) k_grid_layout(GridArgs g) {
             U.x0 = ux0; U.z0 = uz0; U.cell = cell; U.inv_cell = 1.0f / cell;
             U.nx = (int)ceilf((ux1 - ux0) / cell) + 1; U.nz = (int)ceilf((uz1 - uz0) / cell) + 1;
         }
-        *g.uni = U;
         g.ctl[2] = (uint32_t)U.nx; g.ctl[3] = (uint32_t)U.nz;
+        // Speculative rebuild: nobody on the host looks at these sizes before the next kernels run, so they are checked here
+        // against what is allocated; a build that does not fit switches every grid off (nx = 0: no kernel reads a cell, every
+        // lookup finds nothing) and says so in ctl[4].  The caller validates after its own synchronisation and rebuilds.
+        uint32_t fail = 0;
+        if (g.speculative) {
+            if (base + 1ull > (unsigned long long)g.cells_alloc) fail |= RTB_GRID_FAIL_CELLS;
+            if (g.ctl[1] > RTB_GRID_MAX_BIG || g.ctl[1] != g.expect_big) fail |= RTB_GRID_FAIL_BIG;
+            if ((unsigned long long)(U.nx + 1) * (unsigned long long)(U.nz + 1) > g.sat_alloc) fail |= RTB_GRID_FAIL_SAT;
+            if (fail) {
+                for (uint32_t l = 0; l < g.n_lights; ++l) { g.lights[l].nx = 0; g.lights[l].nz = 0; g.lights[l].cell_base = 0; }
+                U.nx = 0; U.nz = 0; g.ctl[0] = 0; g.ctl[2] = 0; g.ctl[3] = 0;
+            }
+        }
+        g.ctl[4] = fail;
+        *g.uni = U;
+    }
+}
+
+// After the count pass: the number of entries (64-bit sum of the per-cell counts: the 32-bit scan that produces the offsets
+// wraps silently above 2^32) against what is allocated / addressable.  Too many: every grid is switched off before the fill
+// pass or any lookup can use a wrapped offset.
+__global__ void k_grid_validate(GridArgs g) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const unsigned long long total = *reinterpret_cast<const unsigned long long*>(g.ctl + 6);
+    if (total > g.entries_alloc || total > 0xfffffff0ull) {
+        g.ctl[4] |= RTB_GRID_FAIL_ENTRIES;
+        for (uint32_t l = 0; l < g.n_lights; ++l) { g.lights[l].nx = 0; g.lights[l].nz = 0; }
+        GridUnion U = *g.uni; U.nx = 0; U.nz = 0; *g.uni = U;
     }
 }
 
 // ---- union occupancy: which plane cells have ANY primitive in ANY light point's grid ------------------------------------
-__global__ void k_grid_union_mark(GridArgs g, uint32_t total_cells) {
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= total_cells || g.cell_start[c + 1] == g.cell_start[c]) return;
+__global__ void k_grid_union_mark(GridArgs g) {
+    const uint32_t total_cells = g.ctl[0];                        // device-side: a speculative build launches for the allocated capacity
+    const GridUnion U = *g.uni;
+    if (U.nx <= 0 || U.nz <= 0) return;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < total_cells; c += gridDim.x * blockDim.x) {
+    if (g.cell_start[c + 1] == g.cell_start[c]) continue;
     uint32_t lo = 0, hi = g.n_lights - 1;                          // the light whose grid holds cell c: last cell_base <= c
     while (lo < hi) {
         const uint32_t mid = (lo + hi + 1) >> 1;
@@ -182,7 +212,7 @@ __global__ void k_grid_union_mark(GridArgs g, uint32_t total_cells) {
     }
     while (lo > 0 && g.lights[lo].nx <= 0) --lo;                   // empty grids share their successor's base
     const GridLight G = g.lights[lo];
-    const GridUnion U = *g.uni;
+    if (G.nx <= 0) continue;
     const uint32_t local = c - G.cell_base;
     const int cz = (int)(local / (uint32_t)G.nx), cx = (int)(local - (uint32_t)cz * (uint32_t)G.nx);
     const float eps = 1e-3f * G.cell;
@@ -192,9 +222,11 @@ __global__ void k_grid_union_mark(GridArgs g, uint32_t total_cells) {
     const uint32_t W = (uint32_t)U.nx + 1;
     for (int z = uz0; z <= uz1; ++z)
         for (int x = ux0; x <= ux1; ++x) g.sat[(uint32_t)(z + 1) * W + (uint32_t)(x + 1)] = 1u;
+    }
 }
 
-__global__ void k_grid_sat_rows(uint32_t* __restrict__ sat, int nx, int nz) {     // one thread per row
+__global__ void k_grid_sat_rows(uint32_t* __restrict__ sat, const GridUnion* __restrict__ uni) {     // one thread per row
+    const int nx = uni->nx, nz = uni->nz;
     const int z = blockIdx.x * blockDim.x + threadIdx.x;
     if (z >= nz) return;
     uint32_t* row = sat + (size_t)(z + 1) * (nx + 1);
@@ -202,7 +234,8 @@ __global__ void k_grid_sat_rows(uint32_t* __restrict__ sat, int nx, int nz) {   
     for (int x = 1; x <= nx; ++x) { acc += row[x]; row[x] = acc; }
 }
 
-__global__ void k_grid_sat_cols(uint32_t* __restrict__ sat, int nx, int nz) {     // one thread per column
+__global__ void k_grid_sat_cols(uint32_t* __restrict__ sat, const GridUnion* __restrict__ uni) {     // one thread per column
+    const int nx = uni->nx, nz = uni->nz;
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     if (x >= nx) return;
     uint32_t acc = 0;
@@ -214,16 +247,19 @@ __global__ void k_grid_sat_cols(uint32_t* __restrict__ sat, int nx, int nz) {   
 template <bool FILL>
 __global__ void k_grid_raster(GridArgs g) {
     const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= (uint64_t)g.n_lights * g.n_tris) return;
-    const uint32_t light = (uint32_t)(t / g.n_tris), prim = (uint32_t)(t - (uint64_t)light * g.n_tris);
-    if (g.prim_flags[prim]) return;
-    const GridLight G = g.lights[light];
-    if (G.nx <= 0 || G.nz <= 0) return;
-    const float4 q0 = g.tris[3 * prim], q1 = g.tris[3 * prim + 1], q2 = g.tris[3 * prim + 2];
-    float x[3], z[3];
-    if (!(grid_project(G.px, G.py, G.pz, G.H, mk3(q0.x, q0.y, q0.z), x[0], z[0]) &&
-          grid_project(G.px, G.py, G.pz, G.H, mk3(q1.x, q1.y, q1.z), x[1], z[1]) &&
-          grid_project(G.px, G.py, G.pz, G.H, mk3(q2.x, q2.y, q2.z), x[2], z[2]))) return;   // cannot happen: such a primitive is flagged
+    uint32_t mine = 0;                                            // cells this thread listed its primitive in (count pass)
+    bool work = t < (uint64_t)g.n_lights * g.n_tris;
+    const uint32_t light = work ? (uint32_t)(t / g.n_tris) : 0u, prim = work ? (uint32_t)(t - (uint64_t)light * g.n_tris) : 0u;
+    work = work && !g.prim_flags[prim];
+    GridLight G = g.lights[light];
+    work = work && G.nx > 0 && G.nz > 0;
+    float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0, q2 = q0;
+    if (work) { q0 = g.tris[3 * prim]; q1 = g.tris[3 * prim + 1]; q2 = g.tris[3 * prim + 2]; }
+    float x[3] = {0.f, 0.f, 0.f}, z[3] = {0.f, 0.f, 0.f};
+    work = work && grid_project(G.px, G.py, G.pz, G.H, mk3(q0.x, q0.y, q0.z), x[0], z[0]) &&
+           grid_project(G.px, G.py, G.pz, G.H, mk3(q1.x, q1.y, q1.z), x[1], z[1]) &&
+           grid_project(G.px, G.py, G.pz, G.H, mk3(q2.x, q2.y, q2.z), x[2], z[2]);     // (always true here: such a primitive is flagged)
+    if (work) {
     const float bx0 = fminf(fminf(x[0], x[1]), x[2]), bx1 = fmaxf(fmaxf(x[0], x[1]), x[2]);
     const float bz0 = fminf(fminf(z[0], z[1]), z[2]), bz1 = fmaxf(fmaxf(z[0], z[1]), z[2]);
     const float m = grid_margin(G.cell, fmaxf(fmaxf(fabsf(bx0), fabsf(bx1)), fmaxf(fabsf(bz0), fabsf(bz1))), G.px, G.pz, G.H);
@@ -274,11 +310,17 @@ __global__ void k_grid_raster(GridArgs g) {
                 uint32_t pos;
                 if (cnt >= 65536u || (use_edges && covers)) pos = beg + (atomicAdd(g.cell_fill + cell, 1u) & (cnt >= 65536u ? 0xffffffffu : 0xffffu));
                 else pos = beg + cnt - 1u - (atomicAdd(g.cell_fill + cell, 0x10000u) >> 16);
-                g.entries[pos] = (int)prim;
+                if ((uint64_t)pos < g.entries_alloc) g.entries[pos] = (int)prim;
             } else {
                 atomicAdd(g.cell_fill + cell, 1u);
+                ++mine;
             }
         }
+    }
+    }
+    if (!FILL) {                                                  // 64-bit total of the counts, one atomic per warp
+        const uint32_t tot = __reduce_add_sync(0xffffffffu, mine);
+        if ((threadIdx.x & 31) == 0 && tot) atomicAdd(reinterpret_cast<unsigned long long*>(g.ctl + 6), (unsigned long long)tot);
     }
 }
 
@@ -518,9 +560,249 @@ __global__ void __launch_bounds__(256, RTB_GRID_BLOCKS) k_shadow_grid(const Trac
     }
 }
 
+// ---- the shadow kernel, second form: ray table and work queues in shared memory ---------------------------------------------------
+// k_shadow_grid keeps every ray in the registers of the lane that set it up and deals tests out round by round: the cursor, the
+// share and the verdict of every ray travel through shared memory and warp votes each round, per light sample of the ticket --
+// a third of its instructions (ncu, profiles/r2a: no source line above 8 %, 680 thread instructions per traced ray for 1.5
+// Moller-Trumbore tests).  Here a ticket is (32 consecutive queued hit points) x (R consecutive light samples) = 32 R rays whose
+// state lives in SHARED memory from the start, and the work is organised as three dense stages over queues of ray ids:
+//   1. lookup     lane = hit point, R cell lookups; a ray with a non-empty cell gets {cursor, remaining} in the ray table and
+//                 its id in the test queue (59 % of the rays of big_bunny's queued hit points; the others are finished)
+//   2. normalise  lane = queued ray: the exact direction and length (Ray::new, src/main.rs:201-202) only for rays that have
+//                 something to test
+//   3. test       lane = next ray of the queue (or, when fewer than 17 are left, a power-of-two share of candidates per ray):
+//                 one prim_mt_q; a miss advances the ray's cursor IN the table and re-queues the ray, a hit moves it to the
+//                 confirm queue, whose entries run prim_confirm_q 32 at a time.
+// No per-sample loops, no owner lane, no verdict round trip; the same exact expressions decide every (ray, primitive) pair.
+#ifndef RTB_GRID2_R
+#define RTB_GRID2_R 4
+#endif
+#ifndef RTB_GRID2_BLOCKS
+#define RTB_GRID2_BLOCKS 4
+#endif
+template <bool COUNT, int R>
+__global__ void __launch_bounds__(256, RTB_GRID2_BLOCKS) k_shadow_grid2(const TraceArgs a) {
+    constexpr int NR = 32 * R;                                   // rays per ticket
+    constexpr int RING = NR <= 64 ? 64 : NR <= 128 ? 128 : NR <= 256 ? 256 : 512;
+    constexpr uint32_t QM = RING - 1;
+    static_assert(NR <= RING, "ring too small");
+    __shared__ float4 s_o[8][32];                                // {o, self primitive} per hit point
+    __shared__ uint32_t s_base[8][32];                           // light-point index of sample 0 per hit point
+    __shared__ float4 s_dL[8][NR];                               // {d, L} per ray
+    __shared__ uint2 s_cr[8][NR];                                // {next entry, entries left} per ray
+    __shared__ uint2 s_tent[8][NR];                              // a candidate that passed prim_mt_q: {primitive, t}
+    __shared__ uint16_t s_q[8][RING], s_q3[8][NR];               // test queue (ring), confirm queue (stack)
+    __shared__ uint32_t s_occ[8][R];                             // result: bit (hit point) of word (sample)
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, lt = (1u << lane) - 1u;
+    const uint32_t n_items = a.queue_ctl[0];
+    const uint32_t groups = (a.nb_light_sample + R - 1) / R;
+    const uint32_t total = ((n_items + 31) / 32) * groups;
+    uint32_t n_box = 0, n_tri = 0, overflow = 0;
+    for (;;) {
+        uint32_t tk = 0;
+        if (lane == 0) tk = atomicAdd(a.queue_ctl + 8, 1u);
+        tk = __shfl_sync(0xffffffffu, tk, 0);
+        if (tk >= total) break;
+        const uint32_t blk = tk / groups, i0 = (tk - blk * groups) * R;
+        const uint32_t it = blk * 32 + lane;
+        // ---- 1. lookups ------------------------------------------------------------------------------------------------------
+        if (lane < R) s_occ[w][lane] = 0u;
+        uint32_t walk = 0, below = 0, queued = 0;                    // bit r: ray r of this lane
+        int self_prim = -1;
+        f3 o = mk3(0.0f, 0.0f, 0.0f);
+        uint32_t base_idx = 0;
+        if (it < n_items) {
+            const float4* ip = a.items + RTB_ITEM_F4 * (size_t)it;
+            const float4 it0 = __ldg(ip), it1 = __ldg(ip + 1);
+            self_prim = (int)(__float_as_uint(it0.y) & RTB_PRIM_MASK);
+            o = mk3(it1.x, it1.y, it1.z);
+            base_idx = __float_as_uint(it0.w);
+        }
+        s_o[w][lane] = make_float4(o.x, o.y, o.z, __int_as_float(self_prim));
+        s_base[w][lane] = base_idx;
+        uint32_t tail = 0, head = 0, n3 = 0;                         // warp-uniform queue counters
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            uint32_t cur = 0, rem = 0;
+            if (it < n_items && i0 + r < a.nb_light_sample) {
+                uint32_t idx = base_idx + i0 + r;                            // (r*NB_RAY + i) % len, src/main.rs:194
+                if (idx >= a.n_samples) idx %= a.n_samples;
+                const float4* gp = reinterpret_cast<const float4*>(a.grid_lights + idx);
+                const float4 g0 = __ldg(gp), g1 = __ldg(gp + 1), g2 = __ldg(gp + 2);  // {px,py,pz,H} {x0,z0,cell,inv_cell} {nx,nz,cell_base,-}
+                const float dy = g0.y - o.y;
+                if (dy > RTB_GRID_TAU * g0.w) {                               // hence d.y = rn(dy / L) >= +0
+                    below |= 1u << r;
+                    const float s = g0.w / dy;
+                    const float fx = (fmaf(o.x - g0.x, s, g0.x) - g1.x) * g1.w, fz = (fmaf(o.z - g0.z, s, g0.z) - g1.y) * g1.w;
+                    const int nx = __float_as_int(g2.x), nz = __float_as_int(g2.y);
+                    if (fx >= 0.0f && fz >= 0.0f && fx < (float)nx && fz < (float)nz) {   // false for NaN
+                        const uint32_t cell = __float_as_uint(g2.z) + (uint32_t)fz * (uint32_t)nx + (uint32_t)fx;
+                        cur = __ldg(a.grid_cell_start + cell);
+                        rem = __ldg(a.grid_cell_start + cell + 1) - cur;
+                    }
+                } else {
+                    walk |= 1u << r;
+                }
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, rem > 0u);
+            if (rem > 0u) {
+                const uint32_t ray = (uint32_t)r * 32u + lane;
+                s_cr[w][ray] = make_uint2(cur, rem);
+                s_q[w][(tail + __popc(m & lt)) & QM] = (uint16_t)ray;
+                queued |= 1u << r;
+            }
+            tail += __popc(m);
+        }
+        __syncwarp();
+        // ---- 2. exact directions of the queued rays ----------------------------------------------------------------------------
+        for (uint32_t k = lane; k < tail; k += 32) {
+            const uint32_t ray = s_q[w][k];
+            const float4 ro = s_o[w][ray & 31u];
+            uint32_t idx = s_base[w][ray & 31u] + i0 + (ray >> 5);
+            if (idx >= a.n_samples) idx %= a.n_samples;
+            const float4 lp = __ldg(a.light_pts + idx);
+            float L; f3 d;
+            normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), mk3(ro.x, ro.y, ro.z)), L, d);    // Ray::new + distance (src/main.rs:201-202)
+            s_dL[w][ray] = make_float4(d.x, d.y, d.z, L);
+        }
+        __syncwarp();
+        // ---- 3. tests ------------------------------------------------------------------------------------------------------------
+        for (;;) {
+            const uint32_t n = tail - head;
+            if (n3 >= 32u || (n == 0u && n3 > 0u)) {
+                // confirm: the box / distance half of the test for rays whose candidate passed Moller-Trumbore
+                const uint32_t cnt = n3 < 32u ? n3 : 32u;
+                if (lane < cnt) {
+                    const uint32_t ray = s_q3[w][n3 - cnt + lane];
+                    const uint2 tp = s_tent[w][ray];
+                    const float4 rd = s_dL[w][ray], ro = s_o[w][ray & 31u];
+                    const f3 po = mk3(ro.x, ro.y, ro.z), d = mk3(rd.x, rd.y, rd.z);
+                    const int prim = (int)tp.x;
+                    bool occluded = prim_confirm_q(__ldg(a.tris + 3 * prim), __ldg(a.tris + 3 * prim + 1), __ldg(a.tris + 3 * prim + 2), po, d, rd.w, __uint_as_float(tp.y));
+                    if (!occluded) {                                      // rejected after all (rare): the rest of the list, from the round's start
+                        const uint2 cr = s_cr[w][ray];
+                        for (uint32_t k = 0; k < cr.y && !occluded; ++k) {
+                            const int p2 = __ldg(a.grid_entries + cr.x + k);
+                            if (p2 == __float_as_int(ro.w)) continue;
+                            if (COUNT) n_tri += 1;
+                            occluded = prim_occludes(a.tris, p2, false, po, d, rd.w, nullptr);
+                        }
+                    }
+                    if (occluded) atomicOr(&s_occ[w][ray >> 5], 1u << (ray & 31u));
+                }
+                n3 -= cnt;
+                __syncwarp();
+                continue;
+            }
+            if (n == 0u) break;
+            const uint32_t sh = n > 16u ? 0u : n > 8u ? 1u : n > 4u ? 2u : n > 2u ? 3u : n > 1u ? 4u : 5u;     // share = 1 << sh candidates per ray
+            const uint32_t slots = n < (32u >> sh) ? n : (32u >> sh);
+            const uint32_t rank = lane >> sh, off = lane & ((1u << sh) - 1u);
+            const bool active = rank < slots;
+            bool hit = false; int prim = -1; float t = 0.0f; uint32_t ray = 0; uint2 cr = make_uint2(0u, 0u);
+            if (active) {
+                ray = s_q[w][(head + rank) & QM];
+                cr = s_cr[w][ray];
+                if (off < cr.y) {
+                    prim = __ldg(a.grid_entries + cr.x + off);
+                    const float4 ro = s_o[w][ray & 31u];
+                    if (prim != __float_as_int(ro.w)) {                              // the hit primitive: k_shade's per-ray self test
+                        const float4 q0 = __ldg(a.tris + 3 * prim), q1 = __ldg(a.tris + 3 * prim + 1), q2 = __ldg(a.tris + 3 * prim + 2);
+                        const f3 po = mk3(ro.x, ro.y, ro.z);
+                        if (!prim_below_origin(q0, q1, q2, po)) {
+                            const float4 rd = s_dL[w][ray];
+                            if (COUNT) n_tri += 1;
+                            hit = prim_mt_q(q0, q1, q2, po, mk3(rd.x, rd.y, rd.z), t);
+                        }
+                    }
+                }
+            }
+            head += slots;
+            const unsigned hm = __ballot_sync(0xffffffffu, hit);
+            const uint32_t seg = (hm >> (rank << sh)) & (sh == 5u ? 0xffffffffu : ((1u << (1u << sh)) - 1u));     // hits among this ray's lanes
+            if (hit && !(seg & ((1u << off) - 1u))) s_tent[w][ray] = make_uint2((uint32_t)prim, __float_as_uint(t));    // lowest hit lane of the ray
+            const bool leader = active && off == 0u;
+            bool cont = false;
+            if (leader && seg == 0u) {                                   // no candidate of this round hit: advance the ray's cursor in the table
+                const uint32_t take = cr.y < (1u << sh) ? cr.y : (1u << sh);
+                cr.x += take; cr.y -= take;
+                s_cr[w][ray] = cr;
+                cont = cr.y > 0u;
+            }
+            const unsigned m2 = __ballot_sync(0xffffffffu, cont);
+            if (cont) s_q[w][(tail + __popc(m2 & lt)) & QM] = (uint16_t)ray;
+            tail += __popc(m2);
+            const bool to3 = leader && seg != 0u;
+            const unsigned m3 = __ballot_sync(0xffffffffu, to3);
+            if (to3) s_q3[w][n3 + __popc(m3 & lt)] = (uint16_t)ray;
+            n3 += __popc(m3);
+            __syncwarp();
+        }
+        // ---- 4. what the grids do not cover: un-rasterisable primitives (the ground), origins not clearly below the light point ---
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool valid = it < n_items && i0 + r < a.nb_light_sample;
+            if (!valid) continue;
+            bool occluded = (s_occ[w][r] >> lane) & 1u;
+            const bool need_big = ((below >> r) & 1u) && !occluded && a.grid_n_big > 0u;
+            const bool need_walk = (walk >> r) & 1u;
+            if (!need_big && !need_walk) continue;
+            bool have = (queued >> r) & 1u;
+            float L = 0.0f; f3 d = mk3(0.0f, 0.0f, 0.0f);
+            if (have) { const float4 rd = s_dL[w][r * 32 + lane]; d = mk3(rd.x, rd.y, rd.z); L = rd.w; }
+            bool extra = false;
+            if (need_big) {
+                for (uint32_t k = 0; k < a.grid_n_big && !extra; ++k) {
+                    const int prim = __ldg(a.grid_big + k);
+                    if (prim == self_prim) continue;
+                    const float4 q0 = __ldg(a.tris + 3 * prim), q1 = __ldg(a.tris + 3 * prim + 1), q2 = __ldg(a.tris + 3 * prim + 2);
+                    if (prim_below_origin(q0, q1, q2, o)) continue;
+                    if (!have) {
+                        uint32_t idx = base_idx + i0 + r;
+                        if (idx >= a.n_samples) idx %= a.n_samples;
+                        const float4 lp = __ldg(a.light_pts + idx);
+                        normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);
+                        have = true;
+                    }
+                    if (COUNT) n_tri += 1;
+                    float t;
+                    extra = prim_mt_q(q0, q1, q2, o, d, t) && prim_confirm_q(q0, q1, q2, o, d, L, t);
+                }
+            }
+            if (need_walk) {
+                if (!have) {
+                    uint32_t idx = base_idx + i0 + r;
+                    if (idx >= a.n_samples) idx %= a.n_samples;
+                    const float4 lp = __ldg(a.light_pts + idx);
+                    normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);
+                }
+                extra = lane_anyhit_walk<COUNT>(a, o, d, L, -1, make_cull(o, d), n_box, n_tri, overflow);   // -1: the hit primitive is k_shade's
+            }
+            if (extra) atomicOr(&s_occ[w][r], 1u << lane);
+        }
+        __syncwarp();
+        // transposed mask: one word per (block of 32 hit points, sample), bit = hit point within the block; every word written once
+        if (lane < (uint32_t)R && i0 + lane < a.nb_light_sample) a.masks[(size_t)blk * a.nb_light_sample + i0 + lane] = s_occ[w][lane];
+        __syncwarp();
+    }
+    if (__any_sync(0xffffffffu, overflow != 0) && lane == 0) atomicAdd(a.counters + RTB_CTR_OVERFLOW, 1ull);
+    if (COUNT) {
+        unsigned long long nb = n_box, nt = n_tri;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) { nb += __shfl_down_sync(0xffffffffu, nb, off); nt += __shfl_down_sync(0xffffffffu, nt, off); }
+        if (lane == 0) { atomicAdd(a.counters + RTB_CTR_BOX, nb); atomicAdd(a.counters + RTB_CTR_TRI, nt); }
+    }
+}
+
 cudaError_t rtb_launch_shadow_grid(const TraceArgs& a, bool count, unsigned blocks, cudaStream_t st) {
-    if (count) k_shadow_grid<true><<<blocks, 256, 0, st>>>(a);
-    else k_shadow_grid<false><<<blocks, 256, 0, st>>>(a);
+    if (a.shadow_kernel == 1) {                                  // round-1 form (rtb_scene_options.shadow_kernel / RTB200_SHADOW_KERNEL=1)
+        if (count) k_shadow_grid<true><<<blocks, 256, 0, st>>>(a);
+        else k_shadow_grid<false><<<blocks, 256, 0, st>>>(a);
+    } else {
+        const unsigned b2 = blocks / 8 * RTB_GRID2_BLOCKS;        // blocks = 8 per SM
+        if (count) k_shadow_grid2<true, RTB_GRID2_R><<<b2, 256, 0, st>>>(a);
+        else k_shadow_grid2<false, RTB_GRID2_R><<<b2, 256, 0, st>>>(a);
+    }
     return cudaGetLastError();
 }
 
@@ -529,7 +811,7 @@ __global__ void k_grid_init(unsigned int* __restrict__ lbounds, uint32_t n_light
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n_lights) { lbounds[4 * i] = 0xffffffffu; lbounds[4 * i + 1] = 0xffffffffu; lbounds[4 * i + 2] = 0u; lbounds[4 * i + 3] = 0u; }
     if (i < n_tris) prim_flags[i] = 0u;
-    if (i < 4) ctl[i] = 0u;
+    if (i < 8) ctl[i] = 0u;
 }
 
 #define GRID_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
@@ -572,40 +854,73 @@ cudaError_t rtb_grid_scene_stats(RtbGrid& G, const float4* d_tris, uint32_t n, c
 void rtb_grid_free(RtbGrid& G) {
     cudaFree(G.d_lights); cudaFree(G.d_lbounds); cudaFree(G.d_prim_flags); cudaFree(G.d_cell_start); cudaFree(G.d_cell_fill);
     cudaFree(G.d_entries); cudaFree(G.d_big); cudaFree(G.d_ctl); cudaFree(G.d_cub); cudaFree(G.d_union); cudaFree(G.d_sat);
+    if (G.ev0) cudaEventDestroy(G.ev0);
+    if (G.ev1) cudaEventDestroy(G.ev1);
     memset(&G, 0, sizeof(G));
 }
 
 // Builds the grids for the light points d_light_pts[0..n_lights).  On success G.valid says whether the grid path applies
 // (false: too many light points / primitives, too many un-rasterisable primitives, or the table would be too large).
+//
+// Two forms.  SYNCHRONOUS (first build of a scene, or after a failed speculative one): the host reads the cell and entry
+// totals between the passes (two stream synchronisations) and sizes the arrays from them, with headroom.  SPECULATIVE
+// (allow_spec, and a synchronous build of the same shape exists): the same kernels are enqueued back to back with NO host
+// synchronisation, launched for the allocated capacity and checking themselves against it on the device (GridArgs.speculative);
+// the caller's render kernels follow on the same stream, the caller synchronises once at the end of its frame and then calls
+// rtb_grid_validate: if the build did not fit, the grids had switched themselves off (no out-of-bounds access, but wrong
+// pixels), and the caller rebuilds synchronously and renders the frame again.  A new sample table (light grids) or a new
+// camera pose (camera grid) of the same scene practically always fits the previous capacity.
 static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tris, const float4* d_light_pts, uint32_t n_lights, float y_plane,
-                                 float cell0, bool with_union, cudaStream_t st);
+                                 float cell0, bool with_union, bool allow_spec, cudaStream_t st);
 
 cudaError_t rtb_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, const float4* d_light_pts, uint32_t n_lights, float cell_factor,
-                           cudaStream_t st) {
-    G.valid = false; G.n_lights = n_lights; G.n_big = 0; G.total_cells = 0; G.total_entries = 0; G.build_ms = 0.0f;
+                           bool allow_spec, cudaStream_t st) {
+    G.valid = false; G.n_lights = n_lights; G.n_big = 0; G.total_cells = 0; G.total_entries = 0; G.build_ms = 0.0f; G.pending = false;
     if (!G.stats_ok) return cudaSuccess;
     // the plane sits a little below the lowest vertex so that ground-level origins project with a finite scale
-    return grid_build_ex(G, d_tris, n_tris, d_light_pts, n_lights, G.y_min - 1.0f - 1e-3f * fabsf(G.y_min), G.mean_extent * cell_factor, true, st);
+    return grid_build_ex(G, d_tris, n_tris, d_light_pts, n_lights, G.y_min - 1.0f - 1e-3f * fabsf(G.y_min), G.mean_extent * cell_factor, true, allow_spec, st);
+}
+
+// After the stream has been synchronised by the caller: the verdict of a pending speculative build.  *ok = false: the grids
+// were switched off on the device and everything rendered with them must be redone after a synchronous build.
+cudaError_t rtb_grid_validate(RtbGrid& G, cudaStream_t st, bool* ok) {
+    *ok = true;
+    if (!G.pending) return cudaSuccess;
+    G.pending = false;
+    uint32_t h_ctl[8];
+    GRID_CK(cudaMemcpyAsync(h_ctl, G.d_ctl, sizeof(h_ctl), cudaMemcpyDeviceToHost, st));
+    GRID_CK(cudaStreamSynchronize(st));
+    if (h_ctl[4]) {
+        static const bool dbg = getenv("RTB200_GRID_DEBUG") != nullptr;
+        if (dbg) fprintf(stderr, "rtb200 grid: speculative build failed (bits %u): synchronous rebuild\n", h_ctl[4]);
+        G.valid = false; G.spec_ok = false; G.spec_failures++;
+        *ok = false;
+        return cudaSuccess;
+    }
+    unsigned long long total; memcpy(&total, h_ctl + 6, 8);
+    G.total_cells = h_ctl[0]; G.n_big = h_ctl[1]; G.total_entries = (uint32_t)total;
+    if (cudaEventElapsedTime(&G.build_ms, G.ev0, G.ev1) != cudaSuccess) { G.build_ms = 0.0f; cudaGetLastError(); }
+    return cudaSuccess;
 }
 
 static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tris, const float4* d_light_pts, uint32_t n_lights, float y_plane,
-                                 float cell0, bool with_union, cudaStream_t st) {
-    G.valid = false; G.n_lights = n_lights; G.n_big = 0; G.total_cells = 0; G.total_entries = 0; G.build_ms = 0.0f;
+                                 float cell0, bool with_union, bool allow_spec, cudaStream_t st) {
+    G.valid = false; G.n_lights = n_lights; G.n_big = 0; G.total_cells = 0; G.total_entries = 0; G.build_ms = 0.0f; G.pending = false;
     const uint64_t work = (uint64_t)n_lights * n_tris;
     static const bool dbg = getenv("RTB200_GRID_DEBUG") != nullptr;
     if (!(cell0 > 0.0f) || n_lights == 0 || n_lights > RTB_GRID_MAX_LIGHTS || n_tris == 0 || work > (256ull << 20)) {
         if (dbg) fprintf(stderr, "rtb200 grid: not applicable (cell0 %g, lights %u, tris %u, work %llu)\n", cell0, n_lights, n_tris, (unsigned long long)work);
+        G.spec_ok = false;
         return cudaSuccess;
     }
-    const size_t CELL_CAP = 64u << 20, ENTRY_CAP = 512u << 20;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    GRID_CK(cudaEventCreate(&ev0)); GRID_CK(cudaEventCreate(&ev1));
-    GRID_CK(cudaEventRecord(ev0, st));
+    const size_t CELL_CAP = 64u << 20;
+    const uint64_t ENTRY_CAP = G.entry_cap_limit ? G.entry_cap_limit : (512ull << 20);
+    if (!G.ev0) { GRID_CK(cudaEventCreate(&G.ev0)); GRID_CK(cudaEventCreate(&G.ev1)); }
     GRID_CK(grid_reserve(&G.d_lights, &G.lights_cap, (size_t)n_lights));
     GRID_CK(grid_reserve(&G.d_lbounds, &G.lbounds_cap, (size_t)n_lights * 4));
     GRID_CK(grid_reserve(&G.d_prim_flags, &G.flags_cap, (size_t)n_tris));
     GRID_CK(grid_reserve(&G.d_big, &G.big_cap, (size_t)RTB_GRID_MAX_BIG));
-    GRID_CK(grid_reserve(&G.d_ctl, &G.ctl_cap, (size_t)4));
+    GRID_CK(grid_reserve(&G.d_ctl, &G.ctl_cap, (size_t)8));
     GRID_CK(grid_reserve(&G.d_union, &G.union_cap, (size_t)1));
     GridArgs g; memset(&g, 0, sizeof(g));
     g.tris = d_tris; g.n_tris = n_tris; g.light_pts = d_light_pts; g.n_lights = n_lights;
@@ -613,9 +928,51 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     g.cell0 = cell0;
     g.lights = G.d_lights; g.lbounds = G.d_lbounds; g.prim_flags = G.d_prim_flags; g.big_list = G.d_big; g.ctl = G.d_ctl; g.uni = G.d_union;
     g.cell_cap = (uint32_t)CELL_CAP;
-    const unsigned nmax = n_lights > n_tris ? n_lights : n_tris;
+    const unsigned nmax = n_lights > n_tris ? (n_lights > 8 ? n_lights : 8) : (n_tris > 8 ? n_tris : 8);
     const unsigned gw = (unsigned)((work + 255) / 256);
-    uint32_t h_ctl[4] = {0, 0, 0, 0};
+    G.builds++;
+
+    // ---- speculative form -------------------------------------------------------------------------------------------------
+    const bool spec = allow_spec && G.spec_ok && G.spec_n_tris == n_tris && G.spec_with_union == with_union && G.spec_y_plane == y_plane &&
+                      G.cell_start_cap > 1 && G.entries_cap > 1 && (!with_union || G.sat_cap > 0);
+    if (spec) {
+        g.cell0 = G.spec_cell0;
+        const bool force_fail = getenv("RTB200_SPEC_FAIL") != nullptr;             // tests: every speculative build "does not fit"
+        g.speculative = 1u; g.cells_alloc = force_fail ? 1u : (uint32_t)G.cell_start_cap; g.expect_big = G.n_big = G.spec_n_big_;
+        g.sat_alloc = G.sat_cap; g.entries_alloc = G.entries_cap < ENTRY_CAP ? G.entries_cap : ENTRY_CAP;
+        g.cell_start = G.d_cell_start; g.cell_fill = G.d_cell_fill; g.entries = G.d_entries; g.sat = G.d_sat;
+        GRID_CK(cudaEventRecord(G.ev0, st));
+        k_grid_init<<<(nmax + 255) / 256, 256, 0, st>>>(G.d_lbounds, n_lights, G.d_prim_flags, n_tris, G.d_ctl);
+        k_grid_classify<<<gw, 256, 0, st>>>(g);
+        k_grid_biglist<<<(n_tris + 255) / 256, 256, 0, st>>>(g);
+        k_grid_layout<<<1, 1024, 0, st>>>(g);
+        const size_t nc = G.cell_start_cap;                       // scan the whole allocation: cells beyond the total hold zero counts
+        GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
+        k_grid_raster<false><<<gw, 256, 0, st>>>(g);
+        size_t need = 0;
+        GRID_CK(cub::DeviceScan::ExclusiveSum(nullptr, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
+        if (need > G.cub_bytes) { cudaFree(G.d_cub); G.d_cub = nullptr; G.cub_bytes = 0; GRID_CK(cudaMalloc(&G.d_cub, need)); G.cub_bytes = need; }
+        GRID_CK(cub::DeviceScan::ExclusiveSum(G.d_cub, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
+        k_grid_validate<<<1, 32, 0, st>>>(g);
+        GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
+        k_grid_raster<true><<<gw, 256, 0, st>>>(g);
+        if (with_union) {
+            GRID_CK(cudaMemsetAsync(G.d_sat, 0, G.sat_cap * sizeof(uint32_t), st));
+            k_grid_union_mark<<<148 * 8, 256, 0, st>>>(g);
+            k_grid_sat_rows<<<(RTB_GRID_UNION_DIM + 1 + 127) / 128, 128, 0, st>>>(G.d_sat, G.d_union);
+            k_grid_sat_cols<<<(RTB_GRID_UNION_DIM + 1 + 127) / 128, 128, 0, st>>>(G.d_sat, G.d_union);
+        }
+        GRID_CK(cudaGetLastError());
+        GRID_CK(cudaEventRecord(G.ev1, st));
+        G.pending = true; G.valid = true; G.spec_builds++;
+        return cudaSuccess;
+    }
+
+    // ---- synchronous form -------------------------------------------------------------------------------------------------
+    G.spec_ok = false;
+    g.speculative = 0u; g.entries_alloc = ENTRY_CAP;
+    GRID_CK(cudaEventRecord(G.ev0, st));
+    uint32_t h_ctl[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     // A primitive that would cover more than RTB_GRID_MAX_CELLS_PER_PRIM cells of some light's grid goes to the `big` list every
     // ray tests.  That is meant for the ground; in a wide scene (64 bunnies over 1600 x 1400 units) the stretched projections of
     // distant primitives cross the limit by the thousand at the cell size the primitives' own extent suggests.  Coarser cells
@@ -634,10 +991,11 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     }
     G.total_cells = h_ctl[0]; G.n_big = h_ctl[1];
     if (dbg) fprintf(stderr, "rtb200 grid: %u lights, %u cells, %u big primitives (max %u)\n", n_lights, G.total_cells, G.n_big, (unsigned)RTB_GRID_MAX_BIG);
-    if (G.n_big > RTB_GRID_MAX_BIG || G.total_cells > CELL_CAP) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return cudaSuccess; }
-    const size_t nc = (size_t)G.total_cells + 1;
-    GRID_CK(grid_reserve(&G.d_cell_start, &G.cell_start_cap, nc));
-    GRID_CK(grid_reserve(&G.d_cell_fill, &G.cell_fill_cap, nc));
+    if (G.n_big > RTB_GRID_MAX_BIG || G.total_cells > CELL_CAP) return cudaSuccess;
+    // headroom: the next table / camera pose of this scene should fit without a synchronous rebuild
+    const size_t nc = (size_t)G.total_cells + 1, nc_alloc = nc + nc / 4 + 1024;
+    GRID_CK(grid_reserve(&G.d_cell_start, &G.cell_start_cap, nc_alloc));
+    GRID_CK(grid_reserve(&G.d_cell_fill, &G.cell_fill_cap, G.cell_start_cap));
     g.cell_start = G.d_cell_start; g.cell_fill = G.d_cell_fill;
     GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
     k_grid_raster<false><<<gw, 256, 0, st>>>(g);
@@ -646,35 +1004,37 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     GRID_CK(cub::DeviceScan::ExclusiveSum(nullptr, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
     if (need > G.cub_bytes) { cudaFree(G.d_cub); G.d_cub = nullptr; G.cub_bytes = 0; GRID_CK(cudaMalloc(&G.d_cub, need)); G.cub_bytes = need; }
     GRID_CK(cub::DeviceScan::ExclusiveSum(G.d_cub, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
-    uint32_t h_total = 0;
-    GRID_CK(cudaMemcpyAsync(&h_total, G.d_cell_start + G.total_cells, sizeof(h_total), cudaMemcpyDeviceToHost, st));
+    // the entry total as a 64-bit sum (k_grid_raster<false>): the 32-bit scan above wraps silently beyond 2^32 entries, and an
+    // array sized from a wrapped total would be written out of bounds by the fill pass
+    unsigned long long h_total = 0;
+    GRID_CK(cudaMemcpyAsync(&h_total, G.d_ctl + 6, sizeof(h_total), cudaMemcpyDeviceToHost, st));
     GRID_CK(cudaStreamSynchronize(st));
-    G.total_entries = h_total;
-    if (dbg) fprintf(stderr, "rtb200 grid: %u entries (cap %zu)\n", h_total, ENTRY_CAP);
-    if ((size_t)h_total > ENTRY_CAP) { cudaEventDestroy(ev0); cudaEventDestroy(ev1); return cudaSuccess; }
-    GRID_CK(grid_reserve(&G.d_entries, &G.entries_cap, (size_t)h_total + 1));
-    g.entries = G.d_entries;
+    if (dbg) fprintf(stderr, "rtb200 grid: %llu entries (cap %llu)\n", h_total, (unsigned long long)ENTRY_CAP);
+    if (h_total > ENTRY_CAP || h_total > 0xfffffff0ull) return cudaSuccess;           // the caller takes the list / walk path
+    G.total_entries = (uint32_t)h_total;
+    GRID_CK(grid_reserve(&G.d_entries, &G.entries_cap, (size_t)h_total + (size_t)h_total / 4 + 1024));
+    g.entries = G.d_entries; g.entries_alloc = G.entries_cap;
     GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
     k_grid_raster<true><<<gw, 256, 0, st>>>(g);
     GRID_CK(cudaGetLastError());
     if (with_union) {   // union occupancy + summed-area table
         const int unx = (int)h_ctl[2], unz = (int)h_ctl[3];
         const size_t ns = (size_t)(unx + 1) * (size_t)(unz + 1);
-        GRID_CK(grid_reserve(&G.d_sat, &G.sat_cap, ns));
+        GRID_CK(grid_reserve(&G.d_sat, &G.sat_cap, ns + ns / 4 + 1024));
         g.sat = G.d_sat;
         GRID_CK(cudaMemsetAsync(G.d_sat, 0, ns * sizeof(uint32_t), st));
-        if (G.total_cells) k_grid_union_mark<<<(G.total_cells + 255) / 256, 256, 0, st>>>(g, G.total_cells);
+        if (G.total_cells) k_grid_union_mark<<<148 * 8, 256, 0, st>>>(g);
         if (unx > 0 && unz > 0) {
-            k_grid_sat_rows<<<(unz + 127) / 128, 128, 0, st>>>(G.d_sat, unx, unz);
-            k_grid_sat_cols<<<(unx + 127) / 128, 128, 0, st>>>(G.d_sat, unx, unz);
+            k_grid_sat_rows<<<(unz + 127) / 128, 128, 0, st>>>(G.d_sat, G.d_union);
+            k_grid_sat_cols<<<(unx + 127) / 128, 128, 0, st>>>(G.d_sat, G.d_union);
         }
         GRID_CK(cudaGetLastError());
     }
-    GRID_CK(cudaEventRecord(ev1, st));
-    GRID_CK(cudaEventSynchronize(ev1));
-    GRID_CK(cudaEventElapsedTime(&G.build_ms, ev0, ev1));
-    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    GRID_CK(cudaEventRecord(G.ev1, st));
+    GRID_CK(cudaEventSynchronize(G.ev1));
+    GRID_CK(cudaEventElapsedTime(&G.build_ms, G.ev0, G.ev1));
     G.valid = true;
+    G.spec_ok = true; G.spec_n_tris = n_tris; G.spec_cell0 = g.cell0; G.spec_y_plane = y_plane; G.spec_with_union = with_union; G.spec_n_big_ = G.n_big;
     return cudaSuccess;
 }
 
@@ -697,11 +1057,11 @@ __global__ void k_cam_tris(const float4* __restrict__ tris, uint32_t n, CameraBa
 }
 
 cudaError_t rtb_cam_grid_build(RtbGrid& G, const float4* d_tris, uint32_t n_tris, float4* d_cam_tris, float4* d_origin, const CameraBasis& cam,
-                               float cell_px, cudaStream_t st) {
-    G.valid = false;
+                               float cell_px, bool allow_spec, cudaStream_t st) {
+    G.valid = false; G.pending = false;
     if (n_tris == 0 || !(cam.distance > 0.0f)) return cudaSuccess;
     k_cam_tris<<<(n_tris + 255) / 256, 256, 0, st>>>(d_tris, n_tris, cam, d_cam_tris);
     GRID_CK(cudaMemsetAsync(d_origin, 0, sizeof(float4), st));
     GRID_CK(cudaGetLastError());
-    return grid_build_ex(G, d_cam_tris, n_tris, d_origin, 1, -cam.distance, cell_px, false, st);
+    return grid_build_ex(G, d_cam_tris, n_tris, d_origin, 1, -cam.distance, cell_px, false, allow_spec, st);
 }

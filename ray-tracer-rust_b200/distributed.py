@@ -72,6 +72,9 @@ class PeerFrame:
     access) and its shading kernel stores each pixel straight into rank 0's frame at the pixel's own position
     (RTB_FLAG_FRAME_ROWS).  No send buffers, no collective moving data, no placement pass; the only cross-rank step per
     frame is a one-element all_reduce that orders "every rank's kernel has finished" before rank 0 reads the frame.
+    TWO frames alternate: while rank 0 still reads (copies, encodes) frame N from one buffer, the peers' kernels of frame
+    N + 1 store into the other one; the all_reduce of frame N + 1 -- which rank 0 enqueues after its reads of frame N - 1 on
+    the same stream -- is what orders "rank 0 has finished with buffer (N + 1) % 2" before anybody's frame N + 2 writes it.
     Same interface as BandGather (send / gather() / frame)."""
 
     def __init__(self, width, height, band_rows, rank, world, device, group=None):
@@ -80,33 +83,50 @@ class PeerFrame:
         self.group = group
         self.nbytes = height * width * 3
         self.index = self.device.index or 0
-        handle = torch.zeros(64, dtype=torch.uint8, device=self.device)
         self.owner = rank == 0
-        if self.owner:
-            self.ptr, h = binding.peer_alloc(self.index, self.nbytes)
-            handle.copy_(torch.frombuffer(bytearray(h), dtype=torch.uint8))
-        if world > 1:
-            dist.broadcast(handle, src=0, group=group)
-        if not self.owner:
-            self.ptr = binding.peer_open(self.index, bytes(handle.cpu().numpy().tobytes()))
-        self.frame = torch.as_tensor(_DevicePtr(self.ptr, self.nbytes), device=self.device) if self.owner else None
+        self.ptrs, self.frames = [0, 0], [None, None]
+        for k in range(2):
+            handle = torch.zeros(64, dtype=torch.uint8, device=self.device)
+            if self.owner:
+                self.ptrs[k], h = binding.peer_alloc(self.index, self.nbytes)
+                handle.copy_(torch.frombuffer(bytearray(h), dtype=torch.uint8))
+            if world > 1:
+                dist.broadcast(handle, src=0, group=group)
+            if not self.owner:
+                self.ptrs[k] = binding.peer_open(self.index, bytes(handle.cpu().numpy().tobytes()))
+            if self.owner:
+                self.frames[k] = torch.as_tensor(_DevicePtr(self.ptrs[k], self.nbytes), device=self.device)
+        self.cur = 0
         self.flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.frame_rows = True
 
+    @property
+    def ptr(self):
+        """The buffer the next frame is rendered into."""
+        return self.ptrs[self.cur]
+
+    @property
+    def frame(self):
+        return self.frames[self.cur]
+
     def gather(self):
-        """Stream-ordered: after it, rank 0's self.frame holds the row-major RGB8 frame of every rank's rows."""
+        """Stream-ordered: after it, the returned tensor (rank 0) holds the row-major RGB8 frame of every rank's rows; the next
+        frame goes to the other buffer."""
         if self.world > 1:
             dist.all_reduce(self.flag, group=self.group)
-        return self.frame
+        done = self.frames[self.cur]
+        self.cur ^= 1
+        return done
 
     def close(self):
-        if self.ptr:
+        if self.ptrs[0]:
             torch.cuda.synchronize(self.device)
             if self.world > 1:
                 dist.barrier(group=self.group)           # nobody unmaps / frees while a peer may still write
-            self.frame = None
-            binding.peer_close(self.index, self.ptr, self.owner)
-            self.ptr = 0
+            self.frames = [None, None]
+            for k in range(2):
+                binding.peer_close(self.index, self.ptrs[k], self.owner)
+            self.ptrs = [0, 0]
 
 
 def render_distributed(scene, gather, **params):

@@ -1,7 +1,8 @@
 // build.rs -- the nvcc step BASELINE.json's north_star asks for: compiles the sm_100a CUDA sources of
 // ray-tracer-rust_b200/csrc into librtb200.so and links the crate against it.
 // SOURCE ONLY: this image has no cargo/rustc, so this file is not exercised here; the tested build is
-// ray-tracer-rust_b200/Makefile, which runs the same commands.
+// ray-tracer-rust_b200/Makefile, which runs the same commands on the same file set: BOTH take every csrc/*.cu
+// (tests/test_host.py::test_rust_build_uses_the_makefile_sources checks that neither hard-codes a list).
 use std::env;
 use std::path::PathBuf;
 use std::process::Command;
@@ -13,7 +14,13 @@ fn main() {
     let nvcc = env::var("NVCC").unwrap_or_else(|_| "/usr/local/cuda/bin/nvcc".to_string());
     let arch = ["-gencode", "arch=compute_100a,code=sm_100a"];
     let mut objs = Vec::new();
-    for name in ["rtb_api", "rtb_trace", "rtb_bvh", "rtb_refpair"] {
+    // every csrc/*.cu belongs to the library, exactly as `CU_SRCS := $(wildcard csrc/*.cu)` in the Makefile
+    let mut names: Vec<String> = std::fs::read_dir(pkg.join("csrc")).expect("csrc/ missing")
+        .filter_map(|e| e.ok()).map(|e| e.path())
+        .filter(|p| p.extension().map_or(false, |x| x == "cu"))
+        .map(|p| p.file_stem().unwrap().to_string_lossy().into_owned()).collect();
+    names.sort();
+    for name in names {
         let src = pkg.join("csrc").join(format!("{}.cu", name));
         let obj = out.join(format!("{}.o", name));
         println!("cargo:rerun-if-changed={}", src.display());
@@ -38,6 +45,7 @@ fn main() {
         .status().unwrap().success();
     assert!(ok);
     println!("cargo:rustc-link-search=native={}", out.display());
+    println!("cargo:rerun-if-changed={}", pkg.join("csrc").display());
     println!("cargo:rustc-link-lib=dylib=rtb200");
     println!("cargo:rustc-link-arg=-Wl,-rpath,{}", out.display());
 }

@@ -8,6 +8,10 @@ pub const RTB_OK: i32 = 0;
 pub const RTB_FLAG_COUNTERS: u32 = 1;
 pub const RTB_FLAG_PROFILE: u32 = 2;
 pub const RTB_FLAG_FRAME_ROWS: u32 = 4;
+pub const RTB_FLAG_GATHER_PEER: u32 = 8;
+pub const RTB_TIE_REFERENCE: u32 = 0;
+pub const RTB_TIE_CALLER: u32 = 1;
+pub const RTB_TIE_INDEX: u32 = 2;
 
 #[repr(C)]
 pub struct RtbScene { _private: [u8; 0] }
@@ -23,6 +27,29 @@ pub struct RtbSceneDesc {
 }
 
 #[repr(C)]
+#[derive(Default)]
+pub struct RtbSceneOptions {
+    pub struct_size: u32, pub shadow_mode: i32, pub primary_mode: i32, pub term_mode: i32,
+    pub chunk_rays: u64, pub term_bytes: u64, pub grid_entry_cap: u64,
+    pub grid_cell_factor: f32, pub cam_cell_px: f32, pub cdiv_off: i32, pub trace_chunks: i32,
+    pub shadow_kernel: i32, pub primary_kernel: i32,
+}
+
+#[repr(C)]
+#[derive(Clone, Copy)]
+pub struct RtbCameraPose { pub eye: [f32; 3], pub look_at: [f32; 3], pub up: [f32; 3], pub distance: f32 }
+
+#[repr(C)]
+#[derive(Default)]
+pub struct RtbSequenceStats {
+    pub seconds: f64, pub device_ms: f32, pub frames: u32, pub cam_grid_redo: u32,
+    pub primary_rays: u64, pub shadow_rays: u64,
+}
+
+pub type RtbFrameFn = Option<unsafe extern "C" fn(user: *mut c_void, pose_index: u32, rgb8: *const u8, width: u32, rows: u32)>;
+
+#[repr(C)]
+#[derive(Clone, Copy)]
 pub struct RtbRenderParams {
     pub width: u32, pub height: u32, pub nb_ray: u32, pub nb_light_sample: u32,
     pub eye: [f32; 3], pub look_at: [f32; 3], pub up: [f32; 3], pub distance: f32,
@@ -37,22 +64,33 @@ pub struct RtbStats {
     pub primary_ms: f32, pub shadow_ms: f32, pub shade_ms: f32, pub queued_hits: u32,
     pub queued_groups: u32, pub queued_walks: u32,
     pub grid_cells: u32, pub grid_entries: u32, pub grid_big: u32, pub grid_build_ms: f32,
+    pub grid_rebuilds: u32, pub grid_redo: u32,
 }
 
 #[repr(C)]
 #[derive(Default)]
 pub struct RtbSceneInfo {
     pub n_tris: u32, pub n_nodes: u32, pub max_depth: u32, pub ploc_iterations: u32,
-    pub sah_cost: f32, pub build_ms: f32,
+    pub sah_cost: f32, pub build_ms: f32, pub tie_mode: u32,
 }
 
 #[link(name = "rtb200")]
 extern "C" {
     pub fn rtb_scene_create(desc: *const RtbSceneDesc, out: *mut *mut RtbScene) -> i32;
+    pub fn rtb_scene_create_ex(desc: *const RtbSceneDesc, options: *const RtbSceneOptions, out: *mut *mut RtbScene) -> i32;
     pub fn rtb_scene_destroy(scene: *mut RtbScene);
     pub fn rtb_scene_get_info(scene: *const RtbScene, info: *mut RtbSceneInfo) -> i32;
     pub fn rtb_scene_set_materials(scene: *mut RtbScene, ks_ns: *const f32) -> i32;
     pub fn rtb_scene_set_samples(scene: *mut RtbScene, samples: *const f32, n_pairs: u32) -> i32;
+    pub fn rtb_scene_set_samples_async(scene: *mut RtbScene, samples: *const f32, n_pairs: u32) -> i32;
+    pub fn rtb_scenes_set_samples(scenes: *const *mut RtbScene, n_gpus: u32, samples: *const f32, n_pairs: u32) -> i32;
+    pub fn rtb_render_multi(scenes: *const *mut RtbScene, n_gpus: u32, params: *const RtbRenderParams, rgb8: *mut u8, stats: *mut RtbStats) -> i32;
+    pub fn rtb_render_sequence(scene: *mut RtbScene, params: *const RtbRenderParams, poses: *const RtbCameraPose, n_poses: u32,
+                               frames: *mut u8, png_pattern: *const c_char, on_frame: RtbFrameFn, user: *mut c_void,
+                               stats: *mut RtbSequenceStats) -> i32;
+    pub fn rtb_render_sequence_multi(scenes: *const *mut RtbScene, n_gpus: u32, params: *const RtbRenderParams, poses: *const RtbCameraPose,
+                                     n_poses: u32, frames: *mut u8, png_pattern: *const c_char, stats: *mut RtbSequenceStats) -> i32;
+    pub fn rtb_measure_peaks(device: i32, fp32_tflops: *mut f32, l2_read_gbs: *mut f32, hbm_read_gbs: *mut f32) -> i32;
     pub fn rtb_render(scene: *mut RtbScene, params: *const RtbRenderParams, rgb8: *mut u8, stats: *mut RtbStats) -> i32;
     pub fn rtb_render_device(scene: *mut RtbScene, params: *const RtbRenderParams, d_rgb8: *mut c_void, cuda_stream: *mut c_void) -> i32;
     pub fn rtb_render_pixels(scene: *mut RtbScene, params: *const RtbRenderParams, pixels: *const u32, n_pix: u64,

@@ -81,14 +81,23 @@ def _peer_worker(rank, world, port, w, h, band, q):
         kw = dict(distance=288.0 * w / 1920, nb_ray=2, nb_light_sample=8)
         pf = D.PeerFrame(w, h, band, rank, world, "cuda:0")
         if rank == 0:
-            pf.frame.zero_()
+            for f in pf.frames:
+                f.zero_()
         torch.cuda.synchronize(); dist.barrier()
-        for _ in range(2):                                            # twice: the mapping is reused frame after frame
+        for _ in range(2):                                            # twice: the mappings are reused frame after frame
             frame = D.render_distributed(sc, pf, **kw)
+        # two different poses back to back without waiting in between: frame A must survive the launch of frame B
+        # (a single buffer could show rows of frame N + 1 to a reader of frame N)
+        eyeB, lookB, upB = S2.orbit_pose(40)
+        frameA = D.render_distributed(sc, pf, **kw)
+        frameB = D.render_distributed(sc, pf, eye=eyeB, look_at=lookB, up=upB, **kw)
         torch.cuda.synchronize(); dist.barrier()
         if rank == 0:
             full, _ = sc.render(width=w, height=h, **kw)
-            q.put(bool((frame.cpu().numpy().reshape(h, w, 3) == full).all()))
+            fullB, _ = sc.render(width=w, height=h, eye=eyeB, look_at=lookB, up=upB, **kw)
+            ok = bool((frame.cpu().numpy().reshape(h, w, 3) == full).all()) and bool((frameA.cpu().numpy().reshape(h, w, 3) == full).all()) \
+                and bool((frameB.cpu().numpy().reshape(h, w, 3) == fullB).all()) and frameA.data_ptr() != frameB.data_ptr()
+            q.put(ok)
         pf.close()
     finally:
         dist.destroy_process_group()
@@ -149,3 +158,55 @@ def test_full_size_4k_16spp_band_shares_tile_the_frame(scene):
     pix = S.stratified_pixels(3840, 2160, 97, seed=21)
     g = scene.render_pixels(pix, **kw)
     assert (full[pix[:, 1], pix[:, 0]] == g["rgb8"]).all()
+
+
+def test_full_size_4k_16spp_frame_bytes_against_the_oracle(scene, oracle_big_bunny, big_bunny_inputs):
+    """The bench workload itself: bytes of the FRAME kernel's 3840x2160 / 16 rays-per-pixel output against the oracle, at stratified
+    pixels over the whole frame and at a dense window over the bunny (x 1760-1920, y 980-1060 at 4K: silhouette, self-shadow)."""
+    _, _, smp = big_bunny_inputs
+    kw = dict(width=3840, height=2160, nb_ray=16, nb_light_sample=100)
+    full, st = scene.render(**kw)
+    strat = S.stratified_pixels(3840, 2160, 216, seed=5)                             # 18 x 10 = 180 pixels
+    xs, ys = np.meshgrid(np.arange(1760, 1920, 8), np.arange(980, 1060, 8))          # 20 x 10 = 200 pixels on the bunny
+    pix = np.concatenate([strat, np.stack([xs.ravel(), ys.ravel()], 1)]).astype(np.uint32)
+    o = oracle_big_bunny.render(3840, 2160, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix, nb_ray=16)
+    assert (full[pix[:, 1], pix[:, 0]] == o["rgb8"]).all()
+    on_bunny = (o["prim0"] >= 0) & (o["prim0"] < 4968)
+    assert on_bunny.sum() >= 100, int(on_bunny.sum())
+
+
+def _multi_scenes(n):
+    import rtb200
+    import torch
+    if torch.cuda.device_count() < n:
+        pytest.skip("needs %d GPUs" % n)
+    v, c = S.big_bunny()
+    smp = S.make_samples()
+    scenes = [rtb200.Scene(v, c, device=i) for i in range(n)]
+    rtb200.set_samples_multi(scenes, smp)
+    return scenes
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_render_multi_c_abi_equals_single_gpu(scene, n):
+    """rtb_render_multi (one call, one host thread per device, SURVEY 8b n_gpus): bytes == the 1-GPU frame, with every device
+    copying its rows to the host frame itself and with the rows gathered over NVLink peer stores into device 0's frame."""
+    import rtb200
+    scenes = _multi_scenes(n)
+    for kw in (dict(width=1920, height=1080, nb_ray=1, nb_light_sample=100), dict(width=3840, height=2160, nb_ray=4, nb_light_sample=25),
+               dict(width=333, height=187, distance=60.0, nb_ray=2, nb_light_sample=9, band_rows=8)):
+        want, st1 = scene.render(**kw)
+        got, st = rtb200.render_multi(scenes, **kw)
+        assert (got == want).all(), kw
+        assert st["primary_hits"] == st1["primary_hits"] and st["shadow_occluded"] == st1["shadow_occluded"]
+        got2, _ = rtb200.render_multi(scenes, gather_peer=True, **kw)
+        assert (got2 == want).all(), kw
+    # frame-parallel sequence over the devices
+    poses = [S.orbit_pose(k) for k in range(24)]
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=1, nb_light_sample=16)
+    frames, sq = rtb200.render_sequence_multi(scenes, poses, **kw)
+    assert sq["frames"] == 24
+    for k in range(24):
+        eye, look, up = poses[k]
+        want, _ = scene.render(eye=eye, look_at=look, up=up, **kw)
+        assert (frames[k] == want).all(), k

@@ -1,6 +1,8 @@
 """GPU parity tests (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on the same seeded
 inputs.  Bars: hit masks, hit primitive, hit distance bits, linear colour bits and RGB8 bytes all EXACT (the
 north_star allows +-1 LSB on 0.1 % of channels and grazing-ray mask differences; this design needs neither)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -10,6 +12,7 @@ from oracle import oracle as O
 pytestmark = pytest.mark.gpu
 
 CAM = dict(eye=S.EYE, look_at=S.LOOK_AT, up=S.UP)
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.fixture(scope="module")
@@ -454,3 +457,180 @@ def test_phong_extension_against_cpu_restatement(rtb, big_bunny_inputs, oracle_b
         osc.set_materials(None)
         o2 = osc.render(480, 270, smp, S.EYE, S.LOOK_AT, S.UP, 72.0, S.LIGHT, nb_ray=2, nb_light_sample=12, pixels=pix)
         assert (back[pix[:, 1], pix[:, 0]] == o2["rgb8"]).all()
+
+
+def test_cuda_path_against_independent_numpy_pixels(gpu_big_bunny):
+    """The same independent fixture the oracle is pinned with (tests/golden/make_pixel_golden.py: numpy float32, brute force,
+    no code shared with the oracle): whole render_pixel results of the CUDA path, bit for bit."""
+    from test_oracle import check_against_pixel_golden
+
+    def render(px, cfg):
+        return gpu_big_bunny.render_pixels(px, width=cfg["width"], height=cfg["height"], nb_ray=cfg["nb_ray"],
+                                           nb_light_sample=cfg["nls"], distance=cfg["distance"])
+    assert check_against_pixel_golden(render) >= 20
+
+
+def test_config_3b_distance_576_exact(gpu_big_bunny, oracle_big_bunny, big_bunny_inputs):
+    """BASELINE config 3, secondary row (framing-preserving distance 576 at 3840x2160, 16 rays/pixel): >= 300 oracle
+    pixels, of which a dense block on the bunny and its shadow edge; pixel-list kernel AND the frame kernel's bytes."""
+    _, _, smp = big_bunny_inputs
+    W, H = 3840, 2160
+    pix = S.stratified_pixels(W, H, 240, seed=33)                                   # 144 spread over the frame
+    xs, ys = np.meshgrid(np.arange(1600, 1960, 24), np.arange(800, 1260, 23))       # 15 x 20 over the bunny, its feet and its shadow
+    pix = np.concatenate([pix, np.stack([xs.ravel(), ys.ravel()], 1)]).astype(np.uint32)
+    g = gpu_big_bunny.render_pixels(pix, width=W, height=H, nb_ray=16, distance=576.0)
+    o = oracle_big_bunny.render(W, H, smp, S.EYE, S.LOOK_AT, S.UP, 576.0, S.LIGHT, pixels=pix, nb_ray=16)
+    assert_same(g, o, "config 3b")
+    on_bunny = (g["prim0"] >= 0) & (g["prim0"] < 4968)
+    assert len(pix) >= 300 and on_bunny.sum() >= 100, (len(pix), int(on_bunny.sum()))
+    assert (g["stats"]["shadow_occluded"] > 0)
+    frame, st = gpu_big_bunny.render(width=W, height=H, nb_ray=16, distance=576.0)
+    assert (frame[pix[:, 1], pix[:, 0]] == o["rgb8"]).all()
+
+
+def test_scene_options_struct_selects_the_paths(rtb, oracle_big_bunny, big_bunny_inputs):
+    """rtb_scene_options (no environment variables): list / walk shadow path, BVH primary path, small chunks, term wavefront on,
+    and an entry cap so small that the grids are refused (64-bit entry total) -- all exact."""
+    v, c, smp = big_bunny_inputs
+    pix = S.stratified_pixels(640, 360, 9, seed=12)
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=2, nb_light_sample=12)
+    o = oracle_big_bunny.render(640, 360, smp, S.EYE, S.LOOK_AT, S.UP, 96.0, S.LIGHT, pixels=pix, nb_ray=2, nb_light_sample=12)
+    ref_frame = None
+    for opts in (dict(), dict(shadow_mode=1), dict(primary_mode=1), dict(chunk_rays=6000, term_mode=1), dict(term_mode=-1, cdiv_off=1),
+                 dict(grid_entry_cap=1000), dict(grid_cell_factor=0.5, cam_cell_px=4.0)):
+        sc = rtb.Scene(v, c, **opts)
+        sc.set_samples(smp)
+        g = sc.render_pixels(pix, **kw)
+        assert_same(g, o, "options %r" % (opts,))
+        frame, st = sc.render(**kw)
+        if ref_frame is None:
+            ref_frame = frame
+        assert (frame == ref_frame).all(), opts
+        if opts.get("shadow_mode") == 1 or opts.get("grid_entry_cap"):
+            assert st["grid_cells"] == 0, opts                     # the light grids are not in use
+        elif not opts.get("primary_mode"):
+            assert st["grid_cells"] > 0, opts
+    assert rtb.Scene(v, c).info()["tie_mode"] == rtb.binding.RTB_TIE_REFERENCE
+
+
+def test_speculative_grid_rebuild_and_redo(rtb, big_bunny_inputs, monkeypatch):
+    """A new sample table / camera rebuilds the grids without host synchronisation inside rtb_render (speculative build, validated
+    after the frame); frames must equal those of a scene that builds synchronously, also when the speculative build does not fit
+    its allocation (no headroom) and the frame is redone."""
+    v, c, smp = big_bunny_inputs
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=2, nb_light_sample=20)
+    tables = [smp, S.make_samples(seed=77), S.make_samples(seed=78)]
+    poses = [S.orbit_pose(k) for k in (0, 30, 61)]
+    monkeypatch.setenv("RTB200_NO_SPEC", "1")
+    ref = rtb.Scene(v, c)
+    want = []
+    for t, (eye, look, up) in zip(tables, poses):
+        ref.set_samples(t)
+        want.append(ref.render(eye=eye, look_at=look, up=up, **kw)[0].copy())
+    monkeypatch.delenv("RTB200_NO_SPEC")
+    for headroom in (None, "0"):                                    # "0": every speculative build reports that it did not fit
+        if headroom is not None:
+            monkeypatch.setenv("RTB200_SPEC_FAIL", "1")
+        sc = rtb.Scene(v, c)
+        rebuilds = redo = 0
+        for k, (t, (eye, look, up)) in enumerate(zip(tables, poses)):
+            sc.set_samples(t)
+            got, st = sc.render(eye=eye, look_at=look, up=up, **kw)
+            assert (got == want[k]).all(), (headroom, k)
+            rebuilds += st["grid_rebuilds"]; redo += st["grid_redo"]
+        assert rebuilds >= 6                                        # light grids + camera grid, three times
+        if headroom == "0":
+            assert redo >= 2                                        # every frame after the first was rendered twice
+
+
+def test_render_sequence_equals_blocking_renders(rtb, gpu_big_bunny, big_bunny_inputs, tmp_path, monkeypatch):
+    """rtb_render_sequence over all 120 orbit poses (BASELINE config 5, 1080p) == rtb_render per pose, byte for
+    byte; PNG files written by the encoder pool decode to the same pixels; and once more with every speculative camera-grid
+    rebuild failing its device-side check (RTB200_SPEC_FAIL), so that the pipeline's repair path runs."""
+    from PIL import Image
+    v, c, smp = big_bunny_inputs
+    poses = [S.orbit_pose(k) for k in range(120)]
+    kw = dict(width=S.WIDTH, height=S.HEIGHT, nb_ray=1, nb_light_sample=100)
+    frames, st = gpu_big_bunny.render_sequence(poses, **kw)
+    assert st["frames"] == 120 and frames.shape == (120, S.HEIGHT, S.WIDTH, 3)
+    for k in range(0, 120, 7):
+        eye, look, up = poses[k]
+        want, _ = gpu_big_bunny.render(eye=eye, look_at=look, up=up, **kw)
+        assert (frames[k] == want).all(), k
+    # every frame differs from its neighbour (the camera moved) and pose 0 is the reference camera
+    assert all((frames[k] != frames[k + 1]).any() for k in range(119))
+    pat = str(tmp_path / "f_%04u.png")
+    _, st2 = gpu_big_bunny.render_sequence(poses[:12], png_pattern=pat, **kw)
+    assert st2["frames"] == 12
+    for k in (0, 5, 11):
+        assert (np.asarray(Image.open(pat % k)) == frames[k]).all()
+    monkeypatch.setenv("RTB200_SPEC_FAIL", "1")
+    sc = rtb.Scene(v, c); sc.set_samples(smp)
+    small = dict(width=640, height=360, distance=96.0, nb_ray=1, nb_light_sample=16)
+    f2, st3 = sc.render_sequence(poses[:40], **small)
+    monkeypatch.delenv("RTB200_SPEC_FAIL")
+    for k in range(40):
+        eye, look, up = poses[k]
+        want, _ = gpu_big_bunny.render(eye=eye, look_at=look, up=up, **small)
+        assert (f2[k] == want).all(), k
+    assert st3["cam_grid_redo"] >= 1
+
+
+def test_async_sample_upload(rtb, gpu_big_bunny, big_bunny_inputs):
+    """rtb_scene_set_samples_async from pinned memory: prefix first, rest on the copy stream; same frame as the blocking upload."""
+    import torch
+    v, c, smp = big_bunny_inputs
+    t2 = S.make_samples(seed=4242)
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=2, nb_light_sample=30)
+    ref = rtb.Scene(v, c); ref.set_samples(t2)
+    want, _ = ref.render(**kw)
+    pinned = torch.from_numpy(t2.copy()).pin_memory()
+    sc = rtb.Scene(v, c); sc.set_samples(smp)
+    sc.render(**kw)
+    sc.set_samples_async(pinned.numpy())
+    got, st = sc.render(**kw)
+    assert (got == want).all() and st["grid_rebuilds"] >= 1
+    short = torch.from_numpy(S.make_samples(7919, seed=3)).pin_memory()     # shorter than the prefix: one copy
+    sc.set_samples_async(short.numpy())
+    ref.set_samples(short.numpy())
+    assert (sc.render(**kw)[0] == ref.render(**kw)[0]).all()
+
+
+def test_measured_peaks_are_plausible(rtb):
+    p = rtb.measure_peaks(0)
+    assert 40.0 < p["fp32_tflops"] < 90.0, p           # 148 SMs x 128 lanes x 2 x ~1.9 GHz = 72-75
+    assert 3000.0 < p["l2_read_gbs"] < 40000.0, p
+    assert 2000.0 < p["hbm_read_gbs"] < 9000.0, p
+
+
+def test_rt_main_host_driver(built, gpu_big_bunny, oracle_big_bunny, big_bunny_inputs, tmp_path):
+    """The C++ twin of the reference's main (src/main.rs:319-362): same prints, output.png in the working directory by default,
+    decoded pixels == Scene.render() == the oracle on a pixel subset."""
+    import subprocess
+    from PIL import Image
+    exe = os.path.join(ROOT, "ray-tracer-rust_b200", "rt_main")
+    if not os.path.exists(exe):
+        subprocess.check_call(["make", "-C", os.path.dirname(exe), "rt_main"])
+    obj = os.path.join(ROOT, "assets", "models", "big_bunny.obj")
+    r = subprocess.run([exe, obj, "/nonexistent/file.obj"], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.splitlines()
+    assert lines[0] == "Building scene" and "Rendering..." in lines and "Writting image to disk" in lines      # [sic], src/main.rs:312
+    assert any(l.startswith("Not a valid path") for l in lines)                                                 # src/main.rs:115-121: prints and continues
+    assert any(l.startswith("Rendered in ") for l in lines) and any(l.startswith("Throughput ") for l in lines)
+    img = np.asarray(Image.open(tmp_path / "output.png"))
+    want, _ = gpu_big_bunny.render()
+    assert img.shape == (S.HEIGHT, S.WIDTH, 3) and (img == want).all()
+    _, _, smp = big_bunny_inputs
+    pix = S.stratified_pixels(S.WIDTH, S.HEIGHT, 40, seed=14)
+    o = oracle_big_bunny.render(S.WIDTH, S.HEIGHT, smp, S.EYE, S.LOOK_AT, S.UP, S.DISTANCE, S.LIGHT, pixels=pix)
+    assert (img[pix[:, 1], pix[:, 0]] == o["rgb8"]).all()
+    # --out, a small frame, an orbit of 3 poses through the sequence entry
+    r = subprocess.run([exe, obj, "--width", "320", "--height", "180", "--distance", "48", "--light-samples", "8", "--orbit", "3",
+                        "--out", str(tmp_path / "orb.png")], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    for k in range(3):
+        eye, look, up = S.orbit_pose(k, 3)
+        want, _ = gpu_big_bunny.render(width=320, height=180, distance=48.0, nb_light_sample=8, eye=eye, look_at=look, up=up)
+        got = np.asarray(Image.open(tmp_path / ("orb_%04d.png" % k)))
+        assert (got == want).all(), k

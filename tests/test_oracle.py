@@ -135,3 +135,43 @@ def test_sample_index_is_px_times_width_plus_py(built):
     moved = sc.render(W, H, smp, S.EYE, S.LOOK_AT, S.UP, 20.0, S.LIGHT, pixels=[[px, py]], nb_light_sample=1)
     assert base["hit_count"][0] == 1 and moved["hit_count"][0] == 1
     assert base["t0"][0] != moved["t0"][0]
+
+
+def _golden():
+    return json.load(open(os.path.join(os.path.dirname(__file__), "golden", "pixel_golden.json")))
+
+
+def check_against_pixel_golden(render_pixels):
+    """Shared by the CPU (oracle) and GPU (CUDA path) tests: complete render_pixel results derived in numpy by
+    tests/golden/make_pixel_golden.py, which shares no code with the oracle or the library."""
+    g = _golden()
+    n_total = 0
+    for cfg in g["configs"]:
+        px = np.array([[p["px"], p["py"]] for p in cfg["pixels"]], np.uint32)
+        got = render_pixels(px, cfg)
+        for i, p in enumerate(cfg["pixels"]):
+            what = "%dx%d nb_ray %d pixel (%d,%d) %s" % (cfg["width"], cfg["height"], cfg["nb_ray"], p["px"], p["py"], p["category"])
+            assert int(got["hit_count"][i]) == p["hit_count"], what
+            assert int(got["prim0"][i]) == p["prim0"], what
+            assert int(got["t0"][i:i + 1].view(np.uint32)[0]) == p["t0_bits"], what
+            assert [int(x) for x in got["rgb_lin"][i].view(np.uint32)] == p["rgb_lin_bits"], what
+            assert [int(x) for x in got["rgb8"][i]] == p["rgb8"], what
+        n_total += len(cfg["pixels"])
+    cats = {p["category"] for cfg in g["configs"] for p in cfg["pixels"]}
+    assert n_total >= 20 and {"ground_lit", "umbra", "penumbra", "bunny_lit", "bunny_partial", "silhouette"} <= cats
+    return n_total
+
+
+def test_oracle_against_independent_numpy_pixels(oracle_big_bunny, big_bunny_inputs):
+    """The pin of the oracle: whole pixels (primary hit + 100 shadow rays + ordered accumulate + gamma) bit for bit."""
+    _, _, smp = big_bunny_inputs
+
+    def render(px, cfg):
+        return oracle_big_bunny.render(cfg["width"], cfg["height"], smp, S.EYE, S.LOOK_AT, S.UP, cfg["distance"], S.LIGHT,
+                                       nb_ray=cfg["nb_ray"], nb_light_sample=cfg["nls"], pixels=px)
+    check_against_pixel_golden(render)
+    # and in the oracle's other traversal mode
+    def render_brute(px, cfg):
+        return oracle_big_bunny.render(cfg["width"], cfg["height"], smp, S.EYE, S.LOOK_AT, S.UP, cfg["distance"], S.LIGHT,
+                                       nb_ray=cfg["nb_ray"], nb_light_sample=cfg["nls"], pixels=px, mode=O.MODE_BRUTE)
+    check_against_pixel_golden(render_brute)
