@@ -326,7 +326,7 @@ class Scene:
         return out, out[:, 12:14].copy().view(np.int32)
 
     def counters(self):
-        out = np.zeros(16, np.uint64)
+        out = np.zeros(64, np.uint64)                # the library writes 16 values (diagnostic builds: up to 64)
         _check(lib().rtb_scene_get_counters(self._h, _ptr(out)))
         return out
 

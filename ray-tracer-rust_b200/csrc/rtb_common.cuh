@@ -80,6 +80,7 @@ struct GridArgs {                  // build-time arguments
     uint32_t cells_alloc;          // cell_start / cell_fill entries allocated (total cells + 1 must fit)
     uint32_t expect_big;           // big-list length the caller's kernel arguments assume
     uint64_t sat_alloc, entries_alloc;
+    uint32_t no_cover_order;
 };
 #define RTB_GRID_FAIL_CELLS 1u     // more cells than allocated
 #define RTB_GRID_FAIL_BIG 2u       // big list longer than RTB_GRID_MAX_BIG or different from the expected length
@@ -185,7 +186,10 @@ __device__ __forceinline__ uint32_t rtb_udiv(uint32_t n, uint32_t d, uint32_t ma
 #define RTB_CTR_BOX 3
 #define RTB_CTR_TRI 4
 #define RTB_CTR_OVERFLOW 5
-#define RTB_NUM_CTRS 16   // 6..8: diagnostics of the counters build (k_shadow_queue: node steps of occluded / free rays, occluded rays)
+#ifndef RTB_NUM_CTRS
+#define RTB_NUM_CTRS 16
+#endif
+// 6..8: diagnostics of the counters build (k_shadow_queue: node steps of occluded / free rays, occluded rays)
 #define RTB_CTR_QUEUED 9        // summed over the chunks of a call by k_shade: queued hit points, (hit point, group) pairs, walk pairs
 #define RTB_CTR_PAIRS 10
 #define RTB_CTR_WALKS 11

@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(1024) k_grid_layout(GridArgs g) {
         if (g.speculative) {
             if (base + 1ull > (unsigned long long)g.cells_alloc) fail |= RTB_GRID_FAIL_CELLS;
             if (g.ctl[1] > RTB_GRID_MAX_BIG || g.ctl[1] != g.expect_big) fail |= RTB_GRID_FAIL_BIG;
-            if ((unsigned long long)(U.nx + 1) * (unsigned long long)(U.nz + 1) > g.sat_alloc) fail |= RTB_GRID_FAIL_SAT;
+            if (g.sat && (unsigned long long)(U.nx + 1) * (unsigned long long)(U.nz + 1) > g.sat_alloc) fail |= RTB_GRID_FAIL_SAT;   // (no table: camera grid)
             if (fail) {
                 for (uint32_t l = 0; l < g.n_lights; ++l) { g.lights[l].nx = 0; g.lights[l].nz = 0; g.lights[l].cell_base = 0; }
                 U.nx = 0; U.nz = 0; g.ctl[0] = 0; g.ctl[2] = 0; g.ctl[3] = 0;
@@ -308,7 +308,7 @@ __global__ void k_grid_raster(GridArgs g) {
                 // high half (cells with >= 2^16 entries are filled front to back only).
                 const uint32_t beg = g.cell_start[cell], cnt = g.cell_start[cell + 1] - beg;
                 uint32_t pos;
-                if (cnt >= 65536u || (use_edges && covers)) pos = beg + (atomicAdd(g.cell_fill + cell, 1u) & (cnt >= 65536u ? 0xffffffffu : 0xffffu));
+                if (cnt >= 65536u || (use_edges && covers && !g.no_cover_order)) pos = beg + (atomicAdd(g.cell_fill + cell, 1u) & (cnt >= 65536u ? 0xffffffffu : 0xffffu));
                 else pos = beg + cnt - 1u - (atomicAdd(g.cell_fill + cell, 0x10000u) >> 16);
                 if ((uint64_t)pos < g.entries_alloc) g.entries[pos] = (int)prim;
             } else {
@@ -666,12 +666,20 @@ __global__ void __launch_bounds__(256, RTB_GRID2_BLOCKS) k_shadow_grid2(const Tr
             s_dL[w][ray] = make_float4(d.x, d.y, d.z, L);
         }
         __syncwarp();
+        if (COUNT && RTB_DIAG_GRID && lane == 0) {
+            atomicAdd(a.counters + 16, 1ull); atomicAdd(a.counters + 17, (unsigned long long)tail);
+        }
         // ---- 3. tests ------------------------------------------------------------------------------------------------------------
         for (;;) {
             const uint32_t n = tail - head;
+            if (COUNT && RTB_DIAG_GRID && lane == 0 && n > 0u && !(n3 >= 32u)) {
+                atomicAdd(a.counters + 18, 1ull); atomicAdd(a.counters + 19, (unsigned long long)n);
+                atomicAdd(a.counters + (n >= 32u ? 20 : n > 16u ? 21 : n > 8u ? 22 : n > 4u ? 23 : n > 2u ? 24 : 25), 1ull);
+            }
             if (n3 >= 32u || (n == 0u && n3 > 0u)) {
                 // confirm: the box / distance half of the test for rays whose candidate passed Moller-Trumbore
                 const uint32_t cnt = n3 < 32u ? n3 : 32u;
+                if (COUNT && RTB_DIAG_GRID && lane == 0) { atomicAdd(a.counters + 29, 1ull); atomicAdd(a.counters + 30, (unsigned long long)cnt); }
                 if (lane < cnt) {
                     const uint32_t ray = s_q3[w][n3 - cnt + lane];
                     const uint2 tp = s_tent[w][ray];
@@ -719,6 +727,11 @@ __global__ void __launch_bounds__(256, RTB_GRID2_BLOCKS) k_shadow_grid2(const Tr
             }
             head += slots;
             const unsigned hm = __ballot_sync(0xffffffffu, hit);
+            if (COUNT && RTB_DIAG_GRID) {
+                const unsigned tested = __ballot_sync(0xffffffffu, active && off < cr.y);
+                const unsigned skipped = __ballot_sync(0xffffffffu, active && off < cr.y && prim >= 0 && !hit && t == 0.0f);
+                if (lane == 0) { atomicAdd(a.counters + 26, (unsigned long long)__popc(tested)); atomicAdd(a.counters + 27, (unsigned long long)__popc(hm)); atomicAdd(a.counters + 28, (unsigned long long)__popc(skipped)); }
+            }
             const uint32_t seg = (hm >> (rank << sh)) & (sh == 5u ? 0xffffffffu : ((1u << (1u << sh)) - 1u));     // hits among this ray's lanes
             if (hit && !(seg & ((1u << off) - 1u))) s_tent[w][ray] = make_uint2((uint32_t)prim, __float_as_uint(t));    // lowest hit lane of the ray
             const bool leader = active && off == 0u;
@@ -928,6 +941,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     g.cell0 = cell0;
     g.lights = G.d_lights; g.lbounds = G.d_lbounds; g.prim_flags = G.d_prim_flags; g.big_list = G.d_big; g.ctl = G.d_ctl; g.uni = G.d_union;
     g.cell_cap = (uint32_t)CELL_CAP;
+    g.no_cover_order = getenv("RTB200_NO_COVER_ORDER") ? 1u : 0u;      // experiment: cells filled in arrival order
     const unsigned nmax = n_lights > n_tris ? (n_lights > 8 ? n_lights : 8) : (n_tris > 8 ? n_tris : 8);
     const unsigned gw = (unsigned)((work + 255) / 256);
     G.builds++;

@@ -18,7 +18,8 @@ else:
     v, c = S.big_bunny(); kw = dict(width=3840, height=2160, nb_ray=16, distance=576.0 if cfg == "3b" else 288.0)
 smp = S.make_samples()
 crcs = set()
-for sk, pk in ((1, 1), (2, 1), (1, 2), (2, 2)):
+pairs = [tuple(int(x) for x in pr.split(",")) for pr in os.environ.get("AB_PAIRS", "1,1 2,1 1,2 2,2").split()]
+for sk, pk in pairs:
     sc = rtb200.Scene(v, c, shadow_kernel=sk, primary_kernel=pk, **extra)
     sc.set_samples(smp)
     sc.render(**kw)

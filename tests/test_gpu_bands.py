@@ -86,6 +86,8 @@ def _peer_worker(rank, world, port, w, h, band, q):
         torch.cuda.synchronize(); dist.barrier()
         for _ in range(2):                                            # twice: the mappings are reused frame after frame
             frame = D.render_distributed(sc, pf, **kw)
+        torch.cuda.synchronize(); dist.barrier()
+        first = frame.cpu().numpy().reshape(h, w, 3).copy() if rank == 0 else None
         # two different poses back to back without waiting in between: frame A must survive the launch of frame B
         # (a single buffer could show rows of frame N + 1 to a reader of frame N)
         eyeB, lookB, upB = S2.orbit_pose(40)
@@ -95,7 +97,7 @@ def _peer_worker(rank, world, port, w, h, band, q):
         if rank == 0:
             full, _ = sc.render(width=w, height=h, **kw)
             fullB, _ = sc.render(width=w, height=h, eye=eyeB, look_at=lookB, up=upB, **kw)
-            ok = bool((frame.cpu().numpy().reshape(h, w, 3) == full).all()) and bool((frameA.cpu().numpy().reshape(h, w, 3) == full).all()) \
+            ok = bool((first == full).all()) and bool((frameA.cpu().numpy().reshape(h, w, 3) == full).all()) \
                 and bool((frameB.cpu().numpy().reshape(h, w, 3) == fullB).all()) and frameA.data_ptr() != frameB.data_ptr()
             q.put(ok)
         pf.close()
