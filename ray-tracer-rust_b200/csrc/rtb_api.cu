@@ -21,7 +21,7 @@
 struct RtbBuildInfo { uint32_t n_nodes, max_depth, iterations; float sah_cost, build_ms; };
 cudaError_t rtb_build_scene(const float*, const float*, const int*, uint32_t, float4*, float4*, float4**, int32_t*, RtbBuildInfo*, cudaStream_t);
 cudaError_t rtb_tie_rank_device(const float4* d_tris, uint32_t n, int* d_rank_out, float4* d_colors4, cudaStream_t st);
-cudaError_t rtb_launch_trace(const TraceArgs&, bool, cudaStream_t, cudaEvent_t*);
+cudaError_t rtb_launch_trace(const TraceArgs&, bool, cudaStream_t, cudaEvent_t*, cudaEvent_t);
 cudaError_t rtb_grid_scene_stats(RtbGrid&, const float4*, uint32_t, cudaStream_t);
 cudaError_t rtb_grid_build(RtbGrid&, const float4*, uint32_t, const float4*, uint32_t, float, bool, cudaStream_t);
 cudaError_t rtb_cam_grid_build(RtbGrid&, const float4*, uint32_t, float4*, float4*, const CameraBasis&, float, bool, cudaStream_t);
@@ -94,6 +94,7 @@ struct rtb_scene {
     uint64_t term_bytes;                         // RTB200_TERM_MB: memory per buffer set for the term wavefront (default 1 GiB, 0 = off)
     bool cdiv_off;                               // RTB200_CDIV=0: always the three-operation shared-reciprocal division
     uint32_t tie_mode;                           // RTB_TIE_*
+    uint32_t tune;                               // RTB200_TUNE experiment bits
     uint32_t shadow_kernel, primary_kernel;      // kernel forms (rtb_scene_options / RTB200_SHADOW_KERNEL / RTB200_PRIMARY_KERNEL)
     // asynchronous sample-table upload (rtb_scene_set_samples_async): the prefix the light tables need travels on `stream`,
     // the rest on `copy_stream`; renders make their stream wait for ev_prefix / ev_samples where they need the data
@@ -242,6 +243,7 @@ int rtb_scene_create_ex(const rtb_scene_desc* desc, const rtb_scene_options* opt
     for (uint32_t i = 0; i < desc->n_tris && s->all_grey; ++i)
         s->all_grey = desc->colors[3 * i] == desc->colors[3 * i + 1] && desc->colors[3 * i + 1] == desc->colors[3 * i + 2];
     s->shadow_kernel = opt.shadow_kernel == 1 ? 1u : 2u; s->primary_kernel = opt.primary_kernel == 1 ? 1u : 2u;
+    if (const char* env = getenv("RTB200_TUNE")) s->tune = (uint32_t)atoi(env);
     if (const char* env = getenv("RTB200_SHADOW_KERNEL")) s->shadow_kernel = atoi(env) == 1 ? 1u : 2u;
     if (const char* env = getenv("RTB200_PRIMARY_KERNEL")) s->primary_kernel = atoi(env) == 1 ? 1u : 2u;
     s->trace_chunks = opt.trace_chunks != 0;
@@ -431,7 +433,7 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         a->grid_big = s->grid.d_big; a->grid_n_big = s->grid.n_big;
         a->grid_union = s->grid.d_union; a->grid_sat = s->grid.d_sat;
     }
-    a->shadow_kernel = s->shadow_kernel; a->primary_kernel = s->primary_kernel;
+    a->shadow_kernel = s->shadow_kernel; a->primary_kernel = s->primary_kernel; a->tune = s->tune;
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
     a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;
     a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;
@@ -473,6 +475,7 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
 static int validate_grids(rtb_scene* s, bool* redo) {
     *redo = false;
     bool ok = true;
+    s->grid.fill_async = false;                  // the caller has synchronised: the fill pass is long done
     CUDA_TRY(rtb_grid_validate(s->grid, s->stream, &ok));
     if (!ok) { s->grid.key_set = false; *redo = true; }
     CUDA_TRY(rtb_grid_validate(s->cam_grid, s->stream, &ok));
@@ -626,7 +629,7 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
         CUDA_TRY(cudaMemsetAsync(b.d_queue_ctl, 0, 16 * sizeof(uint32_t), cs));
         cudaEvent_t* ev = nullptr;
         if (timed && s->timed_chunks < RTB_MAX_TIMED_CHUNKS) ev = s->evp + 4 * s->timed_chunks++;
-        CUDA_TRY(rtb_launch_trace(a, count, cs, ev));
+        CUDA_TRY(rtb_launch_trace(a, count, cs, ev, s->grid.fill_async ? s->grid.ev_fill : nullptr));
         if (h_rows && !a.pixel_list && !a.frame_rows) {
             // pinned host frame (rtb_render): the rows of this chunk leave right behind its k_shade, on the chunk's own stream,
             // so the device-to-host copy of one chunk overlaps the kernels of the next
@@ -754,6 +757,7 @@ static int render_core(rtb_scene* s, const rtb_render_params* p, uint8_t* h_rgb8
         }
         rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0, pinned ? h_rgb8 : nullptr, h_frame_rows);
         if (rc != RTB_OK) return rc;
+        if (s->grid.fill_async) CUDA_TRY(cudaStreamWaitEvent(s->stream, s->grid.ev_fill, 0));    // (frames without shadow kernels never waited for it)
         CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
         uint8_t* stage = nullptr;
         if (h_rgb8 && bytes && !pinned) {

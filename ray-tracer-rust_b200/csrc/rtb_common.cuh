@@ -101,6 +101,9 @@ struct RtbGrid {                   // host-side owner of the light grids of one 
     bool pending;                  // a speculative build has been enqueued and not validated yet (rtb_grid_validate)
     uint64_t entry_cap_limit;      // entries above which the grid path is not taken (0 = default 512 Mi); tests lower it
     cudaEvent_t ev0, ev1;          // build time
+    // speculative build: the fill pass runs on `side` next to the caller's primary-ray kernels (which need the union table only,
+    // and that comes from the COUNT pass); the shadow kernels wait for ev_fill (fill_async: not waited for yet)
+    cudaStream_t side; cudaEvent_t ev_count, ev_fill; bool fill_async;
     uint32_t builds, spec_builds, spec_failures;   // statistics
 };
 
@@ -120,6 +123,7 @@ struct TraceArgs {
     const float2* __restrict__ samples;  // n_samples (u,v) pairs
     const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table
     uint32_t frame_rows;                    // 1: rgb8 is the full frame, owned rows go to their own position (RTB_FLAG_FRAME_ROWS)
+    uint32_t tune;                          // experiment bits (RTB200_TUNE): 1 tickets of k_shadow_grid2 by sample group, 2 occluder hints
     uint32_t shadow_kernel, primary_kernel; // kernel forms (rtb_scene_options): 0 / 2 = current, 1 = the round-1 kernels
     const float4* __restrict__ light_pairs; // pair table of the same points (k_light_pairs), 2 float4 per point
     const float* __restrict__ light_box; // 6 floats: component-wise min / max of light_pts[0..n_light_pts)

@@ -244,9 +244,16 @@ __global__ void k_grid_sat_cols(uint32_t* __restrict__ sat, const GridUnion* __r
 
 // ---- passes C / D: conservative rasterisation of every projected primitive into its light point's grid -----------------
 // FILL = false: count per cell (cell_fill);  FILL = true: write the primitive at cell_start[cell] + cursor.
+#ifndef RTB_RASTER_SPLIT
+#define RTB_RASTER_SPLIT 1
+#endif
 template <bool FILL>
 __global__ void k_grid_raster(GridArgs g) {
-    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // RTB_RASTER_SPLIT threads share one (light point, primitive) pair, rows dealt round-robin: the fill pass waits for the position
+    // every atomic returns, so shorter per-thread chains (and more of them in flight) are what makes it faster
+    const uint64_t tt = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t t = tt / RTB_RASTER_SPLIT;
+    const int sub = (int)(tt - t * RTB_RASTER_SPLIT);
     uint32_t mine = 0;                                            // cells this thread listed its primitive in (count pass)
     bool work = t < (uint64_t)g.n_lights * g.n_tris;
     const uint32_t light = work ? (uint32_t)(t / g.n_tris) : 0u, prim = work ? (uint32_t)(t - (uint64_t)light * g.n_tris) : 0u;
@@ -266,49 +273,61 @@ __global__ void k_grid_raster(GridArgs g) {
     int cx0 = (int)floorf((bx0 - m - G.x0) * G.inv_cell), cx1 = (int)floorf((bx1 + m - G.x0) * G.inv_cell);
     int cz0 = (int)floorf((bz0 - m - G.z0) * G.inv_cell), cz1 = (int)floorf((bz1 + m - G.z0) * G.inv_cell);
     cx0 = max(cx0, 0); cz0 = max(cz0, 0); cx1 = min(cx1, G.nx - 1); cz1 = min(cz1, G.nz - 1);
-    // edge functions of the projected triangle, oriented so that the inside is positive; a cell is skipped when its
-    // m-dilated rectangle lies entirely outside one edge.  Slivers (|area| tiny) use the bounding box alone.
-    float ex[3], ez[3], ec[3];
-    const float area = (x[1] - x[0]) * (z[2] - z[0]) - (x[2] - x[0]) * (z[1] - z[0]);
-    const float sgn = area >= 0.0f ? 1.0f : -1.0f;
-    const bool use_edges = fabsf(area) > 1e-6f * (bx1 - bx0 + bz1 - bz0 + 1e-20f) * (bx1 - bx0 + bz1 - bz0 + 1e-20f);
+    // Scan conversion by rows.  A cell belongs to the primitive iff its m-dilated rectangle meets the projected triangle.  For the
+    // row cz that is a statement about x alone: the part of the (convex) triangle inside the dilated slab Z0 <= z <= Z1 projects
+    // onto an x interval [X0, X1] -- the extreme x of the three edges clipped to the slab -- and the cells of the row whose dilated
+    // x range meets that interval are exactly the cells whose rectangle meets the triangle.  Three clipped edges per ROW instead of
+    // three edge functions per CELL of the bounding box, and no cells beyond the triangle's corners.  Rounding (parameters in [0, 1]
+    // to 2^-22, x to a few ulps) is covered by `eps`, itself far below the margin m that makes the rasterisation conservative.
+    // FILL also finds the cells the triangle covers entirely (both z edges of the dilated rectangle inside it) for the ordering below.
+    float xa[3], za[3], dx[3], dz[3], idz[3];
+    float ext = 0.0f;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const int k1 = (k + 1) % 3;
-        ex[k] = -(z[k1] - z[k]) * sgn; ez[k] = (x[k1] - x[k]) * sgn;      // inward normal
-        ec[k] = -(ex[k] * x[k] + ez[k] * z[k]);
+        xa[k] = x[k]; za[k] = z[k]; dx[k] = x[k1] - x[k]; dz[k] = z[k1] - z[k];
+        idz[k] = dz[k] != 0.0f ? 1.0f / dz[k] : 0.0f;
+        ext = fmaxf(ext, fmaxf(fabsf(x[k]), fabsf(z[k])));
     }
-    for (int cz = cz0; cz <= cz1; ++cz) {
-        const float rz0 = G.z0 + cz * G.cell - m, rz1 = G.z0 + (cz + 1) * G.cell + m;
-        for (int cx = cx0; cx <= cx1; ++cx) {
-            bool covers = true;
-            if (use_edges) {
-                const float rx0 = G.x0 + cx * G.cell - m, rx1 = G.x0 + (cx + 1) * G.cell + m;
-                bool out = false;
+    const float eps = 8e-6f * (ext + (bx1 - bx0) + (bz1 - bz0)) + 1e-30f;
+    const float inf = __int_as_float(0x7f800000);
+    for (int cz = cz0 + sub; cz <= cz1; cz += RTB_RASTER_SPLIT) {
+        const float Z0 = G.z0 + cz * G.cell - m - eps, Z1 = G.z0 + (cz + 1) * G.cell + m + eps;
+        float X0 = inf, X1 = -inf;                               // x range of the triangle within the slab
+        float i0lo = inf, i0hi = -inf, i1lo = inf, i1hi = -inf;  // x range of the triangle AT z = Z0 and AT z = Z1 (FILL)
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    // the rectangle corner furthest along the inward normal
-                    const float fx = ex[k] >= 0.0f ? rx1 : rx0, fz = ez[k] >= 0.0f ? rz1 : rz0;
-                    const float e = ex[k] * fx + ez[k] * fz + ec[k];
-                    // rounding of e: a few ulps of the terms; keep the cell unless it is outside by more than that
-                    const float tol = 4e-6f * (fabsf(ex[k] * fx) + fabsf(ez[k] * fz) + fabsf(ec[k]));
-                    out = out || (e < -tol);
-                    if (FILL) {                                                 // the corner least far along it: inside -> the cell is covered
-                        const float gx = ex[k] >= 0.0f ? rx0 : rx1, gz = ez[k] >= 0.0f ? rz0 : rz1;
-                        covers = covers && (ex[k] * gx + ez[k] * gz + ec[k] > tol);
-                    }
-                }
-                if (out) continue;
+        for (int k = 0; k < 3; ++k) {
+            float t0, t1;
+            if (dz[k] != 0.0f) { t0 = (Z0 - za[k]) * idz[k]; t1 = (Z1 - za[k]) * idz[k]; }
+            else { const bool in = za[k] >= Z0 && za[k] <= Z1; t0 = in ? -inf : inf; t1 = in ? inf : inf; }      // a horizontal edge: inside the slab or not
+            const float tlo = fmaxf(fminf(t0, t1), 0.0f), thi = fminf(fmaxf(t0, t1), 1.0f);
+            if (tlo <= thi) {                                    // the edge meets the slab (false for NaN)
+                const float xl = fmaf(tlo, dx[k], xa[k]), xh = fmaf(thi, dx[k], xa[k]);
+                X0 = fminf(X0, fminf(xl, xh)); X1 = fmaxf(X1, fmaxf(xl, xh));
             }
-            const uint32_t cell = G.cell_base + (uint32_t)cz * (uint32_t)G.nx + (uint32_t)cx;
+            if (FILL && dz[k] != 0.0f) {
+                if (t0 >= 0.0f && t0 <= 1.0f) { const float xc = fmaf(t0, dx[k], xa[k]); i0lo = fminf(i0lo, xc); i0hi = fmaxf(i0hi, xc); }
+                if (t1 >= 0.0f && t1 <= 1.0f) { const float xc = fmaf(t1, dx[k], xa[k]); i1lo = fminf(i1lo, xc); i1hi = fmaxf(i1hi, xc); }
+            }
+        }
+        if (!(X0 <= X1)) continue;                               // the triangle does not reach this row
+        int sx0 = (int)floorf((X0 - m - eps - G.x0) * G.inv_cell), sx1 = (int)floorf((X1 + m + eps - G.x0) * G.inv_cell);
+        sx0 = max(sx0, cx0); sx1 = min(sx1, cx1);
+        const float in_lo = fmaxf(i0lo, i1lo) + eps, in_hi = fminf(i0hi, i1hi) - eps;      // covered cells: dilated x range within [in_lo, in_hi]
+        const uint32_t row = G.cell_base + (uint32_t)cz * (uint32_t)G.nx;
+#pragma unroll 4
+        for (int cx = sx0; cx <= sx1; ++cx) {
+            const uint32_t cell = row + (uint32_t)cx;
             if (FILL) {
                 // Order within a cell (a heuristic, any order is correct): primitives whose projection covers the whole
-                // cell go to the front, the others to the back -- a ray that reads the cell is then usually occluded by
-                // the first or second primitive it tests.  One counter, front count in the low and back count in the
+                // cell go to the front, the others to the back -- a ray that reads the cell is then more often occluded by
+                // the first primitive it tests.  One counter, front count in the low and back count in the
                 // high half (cells with >= 2^16 entries are filled front to back only).
+                const float rx0 = G.x0 + cx * G.cell - m, rx1 = G.x0 + (cx + 1) * G.cell + m;
+                const bool covers = rx0 >= in_lo && rx1 <= in_hi && !g.no_cover_order;
                 const uint32_t beg = g.cell_start[cell], cnt = g.cell_start[cell + 1] - beg;
                 uint32_t pos;
-                if (cnt >= 65536u || (use_edges && covers && !g.no_cover_order)) pos = beg + (atomicAdd(g.cell_fill + cell, 1u) & (cnt >= 65536u ? 0xffffffffu : 0xffffu));
+                if (cnt >= 65536u || covers) pos = beg + (atomicAdd(g.cell_fill + cell, 1u) & (cnt >= 65536u ? 0xffffffffu : 0xffffu));
                 else pos = beg + cnt - 1u - (atomicAdd(g.cell_fill + cell, 0x10000u) >> 16);
                 if ((uint64_t)pos < g.entries_alloc) g.entries[pos] = (int)prim;
             } else {
@@ -869,6 +888,9 @@ void rtb_grid_free(RtbGrid& G) {
     cudaFree(G.d_entries); cudaFree(G.d_big); cudaFree(G.d_ctl); cudaFree(G.d_cub); cudaFree(G.d_union); cudaFree(G.d_sat);
     if (G.ev0) cudaEventDestroy(G.ev0);
     if (G.ev1) cudaEventDestroy(G.ev1);
+    if (G.ev_count) cudaEventDestroy(G.ev_count);
+    if (G.ev_fill) cudaEventDestroy(G.ev_fill);
+    if (G.side) cudaStreamDestroy(G.side);
     memset(&G, 0, sizeof(G));
 }
 
@@ -944,6 +966,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     g.no_cover_order = getenv("RTB200_NO_COVER_ORDER") ? 1u : 0u;      // experiment: cells filled in arrival order
     const unsigned nmax = n_lights > n_tris ? (n_lights > 8 ? n_lights : 8) : (n_tris > 8 ? n_tris : 8);
     const unsigned gw = (unsigned)((work + 255) / 256);
+    const unsigned gr = (unsigned)((work * RTB_RASTER_SPLIT + 255) / 256);     // k_grid_raster: RTB_RASTER_SPLIT threads per pair
     G.builds++;
 
     // ---- speculative form -------------------------------------------------------------------------------------------------
@@ -962,14 +985,25 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
         k_grid_layout<<<1, 1024, 0, st>>>(g);
         const size_t nc = G.cell_start_cap;                       // scan the whole allocation: cells beyond the total hold zero counts
         GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
-        k_grid_raster<false><<<gw, 256, 0, st>>>(g);
+        k_grid_raster<false><<<gr, 256, 0, st>>>(g);
         size_t need = 0;
         GRID_CK(cub::DeviceScan::ExclusiveSum(nullptr, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
         if (need > G.cub_bytes) { cudaFree(G.d_cub); G.d_cub = nullptr; G.cub_bytes = 0; GRID_CK(cudaMalloc(&G.d_cub, need)); G.cub_bytes = need; }
         GRID_CK(cub::DeviceScan::ExclusiveSum(G.d_cub, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
         k_grid_validate<<<1, 32, 0, st>>>(g);
-        GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
-        k_grid_raster<true><<<gw, 256, 0, st>>>(g);
+        // The fill pass is what a lookup needs; the union table below needs the offsets only.  With a union table (light grids) the
+        // fill pass therefore goes to a side stream and runs next to whatever the caller enqueues on `st` before it makes its first
+        // kernel that reads cell lists wait for G.ev_fill (rtb_api.cu: between k_primary and the shadow kernel of every chunk).
+        cudaStream_t fs = st;
+        if (with_union && !getenv("RTB200_NO_FILL_OVERLAP")) {
+            if (!G.side) { GRID_CK(cudaStreamCreateWithFlags(&G.side, cudaStreamNonBlocking)); GRID_CK(cudaEventCreateWithFlags(&G.ev_count, cudaEventDisableTiming)); GRID_CK(cudaEventCreateWithFlags(&G.ev_fill, cudaEventDisableTiming)); }
+            GRID_CK(cudaEventRecord(G.ev_count, st));
+            GRID_CK(cudaStreamWaitEvent(G.side, G.ev_count, 0));
+            fs = G.side;
+        }
+        GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), fs));
+        k_grid_raster<true><<<gr, 256, 0, fs>>>(g);
+        if (fs != st) { GRID_CK(cudaEventRecord(G.ev_fill, fs)); G.fill_async = true; }
         if (with_union) {
             GRID_CK(cudaMemsetAsync(G.d_sat, 0, G.sat_cap * sizeof(uint32_t), st));
             k_grid_union_mark<<<148 * 8, 256, 0, st>>>(g);
@@ -1012,7 +1046,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     GRID_CK(grid_reserve(&G.d_cell_fill, &G.cell_fill_cap, G.cell_start_cap));
     g.cell_start = G.d_cell_start; g.cell_fill = G.d_cell_fill;
     GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
-    k_grid_raster<false><<<gw, 256, 0, st>>>(g);
+    k_grid_raster<false><<<gr, 256, 0, st>>>(g);
     GRID_CK(cudaGetLastError());
     size_t need = 0;
     GRID_CK(cub::DeviceScan::ExclusiveSum(nullptr, need, G.d_cell_fill, G.d_cell_start, (int)nc, st));
@@ -1029,7 +1063,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     GRID_CK(grid_reserve(&G.d_entries, &G.entries_cap, (size_t)h_total + (size_t)h_total / 4 + 1024));
     g.entries = G.d_entries; g.entries_alloc = G.entries_cap;
     GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
-    k_grid_raster<true><<<gw, 256, 0, st>>>(g);
+    k_grid_raster<true><<<gr, 256, 0, st>>>(g);
     GRID_CK(cudaGetLastError());
     if (with_union) {   // union occupancy + summed-area table
         const int unx = (int)h_ctl[2], unz = (int)h_ctl[3];
