@@ -65,8 +65,6 @@ typedef struct {
     float cam_cell_px;            /* camera-grid cell size in pixels, 0 = 2                                            RTB200_CAM_CELL */
     int32_t cdiv_off;             /* 1: never the two-operation division by denom                                      RTB200_CDIV=0 */
     int32_t trace_chunks;         /* 1: per-chunk kernel times of profiled renders on stderr                           RTB200_TRACE_CHUNKS */
-    int32_t shadow_kernel;        /* 0 = 2: k_shadow_grid2 (ray table + queues in shared memory); 1: k_shadow_grid      RTB200_SHADOW_KERNEL */
-    int32_t primary_kernel;       /* 0 = 2: k_primary2 (thread per pixel, loop over its rays); 1: k_primary            RTB200_PRIMARY_KERNEL */
 } rtb_scene_options;
 
 /* Per-frame parameters: the compile-time constants of src/main.rs:38-40 and the literals of

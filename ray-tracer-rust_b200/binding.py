@@ -56,8 +56,7 @@ class SceneOptions(C.Structure):
     """rtb_scene_options: the tunables that were environment variables (0 = default)."""
     _fields_ = [("struct_size", C.c_uint32), ("shadow_mode", C.c_int32), ("primary_mode", C.c_int32), ("term_mode", C.c_int32),
                 ("chunk_rays", C.c_uint64), ("term_bytes", C.c_uint64), ("grid_entry_cap", C.c_uint64),
-                ("grid_cell_factor", C.c_float), ("cam_cell_px", C.c_float), ("cdiv_off", C.c_int32), ("trace_chunks", C.c_int32),
-                ("shadow_kernel", C.c_int32), ("primary_kernel", C.c_int32)]
+                ("grid_cell_factor", C.c_float), ("cam_cell_px", C.c_float), ("cdiv_off", C.c_int32), ("trace_chunks", C.c_int32)]
 
 
 class CameraPose(C.Structure):

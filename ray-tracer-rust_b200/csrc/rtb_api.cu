@@ -94,8 +94,6 @@ struct rtb_scene {
     uint64_t term_bytes;                         // RTB200_TERM_MB: memory per buffer set for the term wavefront (default 1 GiB, 0 = off)
     bool cdiv_off;                               // RTB200_CDIV=0: always the three-operation shared-reciprocal division
     uint32_t tie_mode;                           // RTB_TIE_*
-    uint32_t tune;                               // RTB200_TUNE experiment bits
-    uint32_t shadow_kernel, primary_kernel;      // kernel forms (rtb_scene_options / RTB200_SHADOW_KERNEL / RTB200_PRIMARY_KERNEL)
     // asynchronous sample-table upload (rtb_scene_set_samples_async): the prefix the light tables need travels on `stream`,
     // the rest on `copy_stream`; renders make their stream wait for ev_prefix / ev_samples where they need the data
     cudaStream_t copy_stream; cudaEvent_t ev_prefix, ev_samples, ev_idle; bool samples_pending; uint32_t samples_prefix;
@@ -242,10 +240,6 @@ int rtb_scene_create_ex(const rtb_scene_desc* desc, const rtb_scene_options* opt
     s->all_grey = true;
     for (uint32_t i = 0; i < desc->n_tris && s->all_grey; ++i)
         s->all_grey = desc->colors[3 * i] == desc->colors[3 * i + 1] && desc->colors[3 * i + 1] == desc->colors[3 * i + 2];
-    s->shadow_kernel = opt.shadow_kernel == 1 ? 1u : 2u; s->primary_kernel = opt.primary_kernel == 1 ? 1u : 2u;
-    if (const char* env = getenv("RTB200_TUNE")) s->tune = (uint32_t)atoi(env);
-    if (const char* env = getenv("RTB200_SHADOW_KERNEL")) s->shadow_kernel = atoi(env) == 1 ? 1u : 2u;
-    if (const char* env = getenv("RTB200_PRIMARY_KERNEL")) s->primary_kernel = atoi(env) == 1 ? 1u : 2u;
     s->trace_chunks = opt.trace_chunks != 0;
     if (const char* env = getenv("RTB200_TRACE_CHUNKS")) s->trace_chunks = atoi(env) != 0;
     s->cam_cell_px = opt.cam_cell_px > 0.0f ? opt.cam_cell_px : 2.0f;
@@ -433,7 +427,6 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         a->grid_big = s->grid.d_big; a->grid_n_big = s->grid.n_big;
         a->grid_union = s->grid.d_union; a->grid_sat = s->grid.d_sat;
     }
-    a->shadow_kernel = s->shadow_kernel; a->primary_kernel = s->primary_kernel; a->tune = s->tune;
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
     a->width = p->width; a->height = p->height; a->nb_ray = p->nb_ray; a->nb_light_sample = p->nb_light_sample;
     a->world = world; a->rank = world > 1 ? p->rank : 0; a->band_rows = world > 1 ? p->band_rows : p->height;

@@ -80,7 +80,6 @@ struct GridArgs {                  // build-time arguments
     uint32_t cells_alloc;          // cell_start / cell_fill entries allocated (total cells + 1 must fit)
     uint32_t expect_big;           // big-list length the caller's kernel arguments assume
     uint64_t sat_alloc, entries_alloc;
-    uint32_t no_cover_order;
 };
 #define RTB_GRID_FAIL_CELLS 1u     // more cells than allocated
 #define RTB_GRID_FAIL_BIG 2u       // big list longer than RTB_GRID_MAX_BIG or different from the expected length
@@ -123,8 +122,6 @@ struct TraceArgs {
     const float2* __restrict__ samples;  // n_samples (u,v) pairs
     const float4* __restrict__ light_pts;// light sample points, index (r*nb_ray+i) % n_samples, see k_light_table
     uint32_t frame_rows;                    // 1: rgb8 is the full frame, owned rows go to their own position (RTB_FLAG_FRAME_ROWS)
-    uint32_t tune;                          // experiment bits (RTB200_TUNE): 1 tickets of k_shadow_grid2 by sample group, 2 occluder hints
-    uint32_t shadow_kernel, primary_kernel; // kernel forms (rtb_scene_options): 0 / 2 = current, 1 = the round-1 kernels
     const float4* __restrict__ light_pairs; // pair table of the same points (k_light_pairs), 2 float4 per point
     const float* __restrict__ light_box; // 6 floats: component-wise min / max of light_pts[0..n_light_pts)
     const uint16_t* __restrict__ light_perm; // [nb_ray][nb_light_sample] sample at sorted position j (k_light_groups), nullptr = identity

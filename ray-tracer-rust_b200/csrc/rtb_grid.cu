@@ -24,7 +24,8 @@
 #include <cub/cub.cuh>
 
 #define RTB_GRID_TAU 0.02f            // a point is projectable from P if P.y - y > TAU * (P.y - y_plane): magnification <= 50
-#define RTB_GRID_MAX_CELLS_PER_PRIM 4096
+#define RTB_GRID_MAX_CELLS_PER_PRIM 16384   // estimated list entries of one primitive in one light point's grid; above: 'big' list
+#define RTB_GRID_MAX_ROWS_PER_PRIM 2048
 #define RTB_GRID_MAX_DIM 8192
 #define RTB_GRID_UNION_DIM 2048
 
@@ -75,15 +76,29 @@ __global__ void k_grid_classify(GridArgs g) {
                     grid_project(P.x, P.y, P.z, H, mk3(q1.x, q1.y, q1.z), x[1], z[1]) &&
                     grid_project(P.x, P.y, P.z, H, mk3(q2.x, q2.y, q2.z), x[2], z[2]);
     bool in = ok;
+    float est_cells = 0.0f;
     unsigned int ox0 = 0xffffffffu, oz0 = 0xffffffffu, ox1 = 0u, oz1 = 0u;
     if (ok) {
         const float x0 = fminf(fminf(x[0], x[1]), x[2]), x1 = fmaxf(fmaxf(x[0], x[1]), x[2]);
         const float z0 = fminf(fminf(z[0], z[1]), z[2]), z1 = fmaxf(fmaxf(z[0], z[1]), z[2]);
-        const float cells = ((x1 - x0) / g.cell0 + 2.0f) * ((z1 - z0) / g.cell0 + 2.0f);
-        in = cells <= (float)RTB_GRID_MAX_CELLS_PER_PRIM;                              // false for NaN
+        // work of the scan conversion (k_grid_raster): one clipped-edge computation per cell row, one list entry per cell the
+        // dilated triangle touches -- about area / cell^2 + (width + height) / cell + 1.  (The bounding box says little for the long thin
+        // streaks that distant primitives project to.)
+        const float rows = (z1 - z0) / g.cell0 + 2.0f, cols = (x1 - x0) / g.cell0 + 2.0f;
+        const float area = 0.5f * fabsf((x[1] - x[0]) * (z[2] - z[0]) - (x[2] - x[0]) * (z[1] - z[0]));
+        const float cells = area / (g.cell0 * g.cell0) + (rows - 2.0f) + (cols - 2.0f) + 1.0f;     // expected cells a convex shape meets: A / c^2 + (w + h) / c + 1
+        in = cells <= (float)RTB_GRID_MAX_CELLS_PER_PRIM && rows <= (float)RTB_GRID_MAX_ROWS_PER_PRIM;      // false for NaN
+        est_cells = cells;
         if (in) { ox0 = g_f2ord(x0); oz0 = g_f2ord(z0); ox1 = g_f2ord(x1); oz1 = g_f2ord(z1); }
     }
     if (!in) atomicOr(g.prim_flags + prim, 1u);
+    // estimated list entries of the whole build (ctl[8,9], 64-bit): the host coarsens the cells before rasterising anything if the
+    // estimate is beyond its budget (wide scenes whose distant primitives project to long streaks)
+    {
+        const uint32_t est = in ? (uint32_t)est_cells : 0u;
+        const uint32_t tot = __reduce_add_sync(__activemask(), est);
+        if ((threadIdx.x & 31) == (unsigned)(__ffs(__activemask()) - 1) && tot) atomicAdd(reinterpret_cast<unsigned long long*>(g.ctl + 8), (unsigned long long)tot);
+    }
     // one atomic per (warp, light) instead of one per thread: the lanes of a warp are consecutive primitives of (nearly
     // always) one light point, and every thread of a light point updates the same four words
     const unsigned active = __activemask();
@@ -324,7 +339,7 @@ __global__ void k_grid_raster(GridArgs g) {
                 // the first primitive it tests.  One counter, front count in the low and back count in the
                 // high half (cells with >= 2^16 entries are filled front to back only).
                 const float rx0 = G.x0 + cx * G.cell - m, rx1 = G.x0 + (cx + 1) * G.cell + m;
-                const bool covers = rx0 >= in_lo && rx1 <= in_hi && !g.no_cover_order;
+                const bool covers = rx0 >= in_lo && rx1 <= in_hi;
                 const uint32_t beg = g.cell_start[cell], cnt = g.cell_start[cell + 1] - beg;
                 uint32_t pos;
                 if (cnt >= 65536u || covers) pos = beg + (atomicAdd(g.cell_fill + cell, 1u) & (cnt >= 65536u ? 0xffffffffu : 0xffffu));
@@ -377,213 +392,16 @@ __device__ __noinline__ bool lane_anyhit_walk(const TraceArgs& a, f3 o, f3 d, fl
     }
 }
 
-// A warp takes a ticket = (block of 32 consecutive queue slots, RTB_GRID_R consecutive light samples): lane l owns the
-// R rays of hit point l.  32 consecutive slots are a pixel tile of k_primary and a sample index means the same light
-// point for (nearly) all of them, so the lanes read neighbouring cells of one grid.
-//
-// The candidate lists differ in length (most rays of a tile near a shadow edge have none, a few have several) and a ray
-// stops at its first occluder, so a loop per lane leaves two thirds of the lanes idle (ncu, profiles/r1c: 11.8 of 32
-// threads per instruction).  The tests are therefore dealt out anew every round: the A rays that still have candidates
-// and no occluder offer their next `share` candidates (share = 1 when A >= 17, else the power of two <= 32 / A), lane j
-// tests candidate j % share of the (j / share)-th such ray -- its origin, direction and cursor come from shared memory --
-// and the verdicts return with one warp-wide OR per sample.  Only the first half of the test (prim_mt_q) runs in the
-// rounds; a ray that passes it stops offering candidates, and the second half (prim_confirm_q: the leaf box and the
-// distance compare, which hardly ever reject) runs afterwards in the ray's own lane.  If it does reject, the ray walks
-// the rest of its list alone.  Which lane evaluates a (ray, primitive) pair never changes its value.
-// Result: the transposed occlusion masks described at the end of the loop.
 #ifndef RTB_DIAG_GRID
-#define RTB_DIAG_GRID 0      // 1: round statistics in counters 6, 7, 12-15 (scripts/diag_grid.py)
+#define RTB_DIAG_GRID 0      // 1: round statistics of k_shadow_grid in counters 16-30 (scripts/diag_grid2.py; needs -DRTB_NUM_CTRS=32)
 #endif
-#ifndef RTB_GRID_R
-#define RTB_GRID_R 2
-#endif
-#ifndef RTB_GRID_BLOCKS
-#define RTB_GRID_BLOCKS 4       // resident blocks per SM the register allocation aims at
-#endif
-template <bool COUNT>
-__global__ void __launch_bounds__(256, RTB_GRID_BLOCKS) k_shadow_grid(const TraceArgs a) {
-    constexpr int R = RTB_GRID_R;
-    __shared__ float4 s_o[8][32];                        // {o, self primitive}
-    __shared__ float4 s_d[8][R][32];                     // {d, L}
-    __shared__ uint32_t s_cur[8][R][32], s_take[8][R][32];   // next entry (index into grid_entries), entries offered this round
-    __shared__ uint32_t s_src[8][32];                    // rank among the active rays -> r * 32 + lane
-    __shared__ uint2 s_tent[8][R][32];                   // a candidate that passed prim_mt_q: {primitive, t}
-    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, lt = (1u << lane) - 1u;
-    const uint32_t n_items = a.queue_ctl[0];
-    const uint32_t groups = (a.nb_light_sample + R - 1) / R;
-    const uint32_t total = ((n_items + 31) / 32) * groups;
-    uint32_t n_box = 0, n_tri = 0, overflow = 0;
-    for (;;) {
-        uint32_t tk = 0;
-        if (lane == 0) tk = atomicAdd(a.queue_ctl + 8, 1u);
-        tk = __shfl_sync(0xffffffffu, tk, 0);
-        if (tk >= total) break;
-        const uint32_t blk = tk / groups, i0 = (tk - blk * groups) * R;
-        const uint32_t it = blk * 32 + lane;
-        uint32_t cur[R], rem[R];
-        uint32_t occ = 0, walk = 0, below = 0, tent = 0;            // bit r: ray r of this lane
-        int self_prim = -1;
-        f3 o = mk3(0.0f, 0.0f, 0.0f);
-#pragma unroll
-        for (int r = 0; r < R; ++r) { cur[r] = 0; rem[r] = 0; }
-        if (it < n_items) {
-            const float4* ip = a.items + RTB_ITEM_F4 * (size_t)it;
-            const float4 it0 = __ldg(ip), it1 = __ldg(ip + 1);
-            self_prim = (int)(__float_as_uint(it0.y) & RTB_PRIM_MASK);
-            o = mk3(it1.x, it1.y, it1.z);
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if (i0 + r >= a.nb_light_sample) continue;
-                uint32_t idx = __float_as_uint(it0.w) + i0 + r;                  // (r*NB_RAY + i) % len, src/main.rs:194
-                if (idx >= a.n_samples) idx %= a.n_samples;
-                const float4 lp = __ldg(a.light_pts + idx);
-                float L; f3 d;
-                normalize_exact(sub3(mk3(lp.x, lp.y, lp.z), o), L, d);           // Ray::new + distance (src/main.rs:201-202)
-                s_d[w][r][lane] = make_float4(d.x, d.y, d.z, L);
-                const float4* gp = reinterpret_cast<const float4*>(a.grid_lights + idx);
-                const float4 g0 = __ldg(gp), g1 = __ldg(gp + 1), g2 = __ldg(gp + 2);  // {px,py,pz,H} {x0,z0,cell,inv_cell} {nx,nz,cell_base,-}
-                const float dy = g0.y - o.y;
-                if (dy > RTB_GRID_TAU * g0.w) {                                   // hence d.y = rn(dy / L) >= +0
-                    below |= 1u << r;
-                    const float s = g0.w / dy;
-                    const float fx = (fmaf(o.x - g0.x, s, g0.x) - g1.x) * g1.w, fz = (fmaf(o.z - g0.z, s, g0.z) - g1.y) * g1.w;
-                    const int nx = __float_as_int(g2.x), nz = __float_as_int(g2.y);
-                    if (fx >= 0.0f && fz >= 0.0f && fx < (float)nx && fz < (float)nz) {   // false for NaN
-                        const uint32_t cell = __float_as_uint(g2.z) + (uint32_t)fz * (uint32_t)nx + (uint32_t)fx;
-                        cur[r] = __ldg(a.grid_cell_start + cell);
-                        rem[r] = __ldg(a.grid_cell_start + cell + 1) - cur[r];
-                    }
-                } else {
-                    walk |= 1u << r;
-                }
-            }
-        }
-        s_o[w][lane] = make_float4(o.x, o.y, o.z, __int_as_float(self_prim));
-        if (COUNT && RTB_DIAG_GRID) {
-            uint32_t nz_ = 0, sum_ = 0;
-#pragma unroll
-            for (int r = 0; r < R; ++r) { nz_ += rem[r] > 0; sum_ += rem[r]; }
-            for (int off_ = 16; off_ > 0; off_ >>= 1) { sum_ += __shfl_down_sync(0xffffffffu, sum_, off_); nz_ += __shfl_down_sync(0xffffffffu, nz_, off_); }
-            if (lane == 0) { atomicAdd(a.counters + 12, 1ull); atomicAdd(a.counters + 13, (unsigned long long)sum_); atomicAdd(a.counters + 14, (unsigned long long)nz_); }
-        }
-        for (;;) {
-            unsigned act[R]; uint32_t base[R + 1];
-            base[0] = 0;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                act[r] = __ballot_sync(0xffffffffu, rem[r] > 0 && !((tent >> r) & 1u));
-                base[r + 1] = base[r] + __popc(act[r]);
-            }
-            const uint32_t A = base[R];
-            if (!A) break;
-            const uint32_t sh = A > 16 ? 0u : A > 8 ? 1u : A > 4 ? 2u : A > 2 ? 3u : A > 1 ? 4u : 5u;     // share = 1 << sh
-            uint32_t served = 0;                                      // bit r: ray r of this lane is dealt out this round
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if ((act[r] >> lane) & 1u) {
-                    const uint32_t rk = base[r] + __popc(act[r] & lt);
-                    if (rk < 32u) {
-                        served |= 1u << r;
-                        s_src[w][rk] = (uint32_t)r * 32u + lane;
-                        s_cur[w][r][lane] = cur[r];
-                        s_take[w][r][lane] = min(rem[r], 1u << sh);
-                    }
-                }
-            }
-            __syncwarp();
-            const uint32_t rank = lane >> sh, off = lane & ((1u << sh) - 1u);
-            bool hit = false; uint32_t src = 0; int my_prim = -1; float my_t = 0.0f;
-            if (rank < A) {
-                src = s_src[w][rank];
-                const uint32_t sr = src >> 5, sl = src & 31u;
-                if (off < s_take[w][sr][sl]) {
-                    const int prim = __ldg(a.grid_entries + s_cur[w][sr][sl] + off);
-                    const float4 ro = s_o[w][sl];
-                    if (prim != __float_as_int(ro.w)) {                              // the hit primitive: k_shade's per-ray self test
-                        const float4 q0 = __ldg(a.tris + 3 * prim), q1 = __ldg(a.tris + 3 * prim + 1), q2 = __ldg(a.tris + 3 * prim + 2);
-                        const f3 po = mk3(ro.x, ro.y, ro.z);
-                        if (!prim_below_origin(q0, q1, q2, po)) {
-                            const float4 rd = s_d[w][sr][sl];
-                            float t;
-                            if (COUNT) n_tri += 1;
-                            hit = prim_mt_q(q0, q1, q2, po, mk3(rd.x, rd.y, rd.z), t);
-                            if (hit) { s_tent[w][sr][sl].x = (uint32_t)prim; my_prim = prim; my_t = t; }   // several lanes may: one wins
-                        }
-                    }
-                }
-            }
-            __syncwarp();
-            if (hit && s_tent[w][src >> 5][src & 31u].x == (uint32_t)my_prim) s_tent[w][src >> 5][src & 31u].y = __float_as_uint(my_t);   // a cell lists a primitive once
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const unsigned verdict = __reduce_or_sync(0xffffffffu, (hit && (src >> 5) == (uint32_t)r) ? (1u << (src & 31u)) : 0u);
-                if ((served >> r) & 1u) {
-                    if ((verdict >> lane) & 1u) tent |= 1u << r;         // cur[r] stays at the start of this round (see below)
-                    else { const uint32_t take = min(rem[r], 1u << sh); cur[r] += take; rem[r] -= take; }
-                }
-            }
-            if (COUNT && RTB_DIAG_GRID) {
-                const unsigned hits_ = __ballot_sync(0xffffffffu, hit);
-                if (lane == 0) { atomicAdd(a.counters + 6, 1ull); atomicAdd(a.counters + 7, (unsigned long long)A); atomicAdd(a.counters + 15, (unsigned long long)__popc(hits_)); }
-            }
-            __syncwarp();
-        }
-        // second half of the test for the rays that found a candidate, in their own lane; then what the grids do not cover
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const bool valid = it < n_items && i0 + r < a.nb_light_sample;
-            const float4 rd = s_d[w][r][lane];
-            const f3 d = mk3(rd.x, rd.y, rd.z);
-            const float L = rd.w;
-            bool occluded = false;
-            if ((tent >> r) & 1u) {
-                const uint2 tp = s_tent[w][r][lane];
-                const int prim = (int)tp.x;
-                occluded = prim_confirm_q(__ldg(a.tris + 3 * prim), __ldg(a.tris + 3 * prim + 1), __ldg(a.tris + 3 * prim + 2), o, d, L, __uint_as_float(tp.y));
-                for (uint32_t k = 0; k < rem[r] && !occluded; ++k) {              // rejected after all: the rest of the list, from the round's start
-                    const int p2 = __ldg(a.grid_entries + cur[r] + k);
-                    if (p2 == self_prim) continue;
-                    if (COUNT) n_tri += 1;
-                    occluded = prim_occludes(a.tris, p2, false, o, d, L, nullptr);
-                }
-            }
-            if (valid && ((below >> r) & 1u)) {
-                for (uint32_t k = 0; k < a.grid_n_big && !occluded; ++k) {          // primitives outside the grids (the ground)
-                    const int prim = __ldg(a.grid_big + k);
-                    if (prim == self_prim) continue;
-                    const float4 q0 = __ldg(a.tris + 3 * prim), q1 = __ldg(a.tris + 3 * prim + 1), q2 = __ldg(a.tris + 3 * prim + 2);
-                    if (prim_below_origin(q0, q1, q2, o)) continue;
-                    if (COUNT) n_tri += 1;
-                    float t;
-                    occluded = prim_mt_q(q0, q1, q2, o, d, t) && prim_confirm_q(q0, q1, q2, o, d, L, t);
-                }
-            }
-            if ((walk >> r) & 1u) occluded = lane_anyhit_walk<COUNT>(a, o, d, L, -1, make_cull(o, d), n_box, n_tri, overflow);   // -1: the hit primitive is k_shade's
-            if (occluded) occ |= 1u << r;
-        }
-        // transposed mask: one word per (block of 32 hit points, sample), bit = hit point within the block; k_shade reads
-        // bit (slot % 32) of word (slot / 32) * nls + i.  Every word is written exactly once: no atomics, no clearing.
-#pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const unsigned m = __ballot_sync(0xffffffffu, (occ >> r) & 1u);
-            if (lane == 0 && i0 + r < a.nb_light_sample) a.masks[(size_t)blk * a.nb_light_sample + i0 + r] = m;
-        }
-        __syncwarp();
-    }
-    if (__any_sync(0xffffffffu, overflow != 0) && lane == 0) atomicAdd(a.counters + RTB_CTR_OVERFLOW, 1ull);
-    if (COUNT) {
-        unsigned long long nb = n_box, nt = n_tri;
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) { nb += __shfl_down_sync(0xffffffffu, nb, off); nt += __shfl_down_sync(0xffffffffu, nt, off); }
-        if (lane == 0) { atomicAdd(a.counters + RTB_CTR_BOX, nb); atomicAdd(a.counters + RTB_CTR_TRI, nt); }
-    }
-}
 
-// ---- the shadow kernel, second form: ray table and work queues in shared memory ---------------------------------------------------
-// k_shadow_grid keeps every ray in the registers of the lane that set it up and deals tests out round by round: the cursor, the
-// share and the verdict of every ray travel through shared memory and warp votes each round, per light sample of the ticket --
-// a third of its instructions (ncu, profiles/r2a: no source line above 8 %, 680 thread instructions per traced ray for 1.5
-// Moller-Trumbore tests).  Here a ticket is (32 consecutive queued hit points) x (R consecutive light samples) = 32 R rays whose
+// ---- the shadow kernel of the grid path: ray table and work queues in shared memory ---------------------------------------------------
+// The candidate lists differ in length (most rays of a tile near a shadow edge have none, a few have several) and a ray stops at
+// its first occluder, so a loop per lane leaves two thirds of the lanes idle (ncu, profiles/r1c: 11.8 of 32 threads per
+// instruction).  Round 1's kernel kept every ray in the registers of the lane that set it up and dealt the tests out round by
+// round, per light sample (profiles/r2a: 680 thread instructions per traced ray for 1.5 Moller-Trumbore tests, a third of them
+// the dealing).  Here a ticket is (32 consecutive queued hit points) x (R consecutive light samples) = 32 R rays whose
 // state lives in SHARED memory from the start, and the work is organised as three dense stages over queues of ray ids:
 //   1. lookup     lane = hit point, R cell lookups; a ray with a non-empty cell gets {cursor, remaining} in the ray table and
 //                 its id in the test queue (59 % of the rays of big_bunny's queued hit points; the others are finished)
@@ -593,14 +411,14 @@ __global__ void __launch_bounds__(256, RTB_GRID_BLOCKS) k_shadow_grid(const Trac
 //                 one prim_mt_q; a miss advances the ray's cursor IN the table and re-queues the ray, a hit moves it to the
 //                 confirm queue, whose entries run prim_confirm_q 32 at a time.
 // No per-sample loops, no owner lane, no verdict round trip; the same exact expressions decide every (ray, primitive) pair.
-#ifndef RTB_GRID2_R
-#define RTB_GRID2_R 4
+#ifndef RTB_GRID_R
+#define RTB_GRID_R 4
 #endif
-#ifndef RTB_GRID2_BLOCKS
-#define RTB_GRID2_BLOCKS 4
+#ifndef RTB_GRID_BLOCKS
+#define RTB_GRID_BLOCKS 4
 #endif
 template <bool COUNT, int R>
-__global__ void __launch_bounds__(256, RTB_GRID2_BLOCKS) k_shadow_grid2(const TraceArgs a) {
+__global__ void __launch_bounds__(256, RTB_GRID_BLOCKS) k_shadow_grid(const TraceArgs a) {
     constexpr int NR = 32 * R;                                   // rays per ticket
     constexpr int RING = NR <= 64 ? 64 : NR <= 128 ? 128 : NR <= 256 ? 256 : 512;
     constexpr uint32_t QM = RING - 1;
@@ -827,14 +645,9 @@ __global__ void __launch_bounds__(256, RTB_GRID2_BLOCKS) k_shadow_grid2(const Tr
 }
 
 cudaError_t rtb_launch_shadow_grid(const TraceArgs& a, bool count, unsigned blocks, cudaStream_t st) {
-    if (a.shadow_kernel == 1) {                                  // round-1 form (rtb_scene_options.shadow_kernel / RTB200_SHADOW_KERNEL=1)
-        if (count) k_shadow_grid<true><<<blocks, 256, 0, st>>>(a);
-        else k_shadow_grid<false><<<blocks, 256, 0, st>>>(a);
-    } else {
-        const unsigned b2 = blocks / 8 * RTB_GRID2_BLOCKS;        // blocks = 8 per SM
-        if (count) k_shadow_grid2<true, RTB_GRID2_R><<<b2, 256, 0, st>>>(a);
-        else k_shadow_grid2<false, RTB_GRID2_R><<<b2, 256, 0, st>>>(a);
-    }
+    const unsigned b2 = blocks / 8 * RTB_GRID_BLOCKS;        // blocks = 8 per SM
+    if (count) k_shadow_grid<true, RTB_GRID_R><<<b2, 256, 0, st>>>(a);
+    else k_shadow_grid<false, RTB_GRID_R><<<b2, 256, 0, st>>>(a);
     return cudaGetLastError();
 }
 
@@ -843,7 +656,7 @@ __global__ void k_grid_init(unsigned int* __restrict__ lbounds, uint32_t n_light
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n_lights) { lbounds[4 * i] = 0xffffffffu; lbounds[4 * i + 1] = 0xffffffffu; lbounds[4 * i + 2] = 0u; lbounds[4 * i + 3] = 0u; }
     if (i < n_tris) prim_flags[i] = 0u;
-    if (i < 8) ctl[i] = 0u;
+    if (i < 12) ctl[i] = 0u;
 }
 
 #define GRID_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
@@ -948,14 +761,14 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
         G.spec_ok = false;
         return cudaSuccess;
     }
-    const size_t CELL_CAP = 64u << 20;
+    const size_t CELL_CAP = 512u << 20;
     const uint64_t ENTRY_CAP = G.entry_cap_limit ? G.entry_cap_limit : (512ull << 20);
     if (!G.ev0) { GRID_CK(cudaEventCreate(&G.ev0)); GRID_CK(cudaEventCreate(&G.ev1)); }
     GRID_CK(grid_reserve(&G.d_lights, &G.lights_cap, (size_t)n_lights));
     GRID_CK(grid_reserve(&G.d_lbounds, &G.lbounds_cap, (size_t)n_lights * 4));
     GRID_CK(grid_reserve(&G.d_prim_flags, &G.flags_cap, (size_t)n_tris));
     GRID_CK(grid_reserve(&G.d_big, &G.big_cap, (size_t)RTB_GRID_MAX_BIG));
-    GRID_CK(grid_reserve(&G.d_ctl, &G.ctl_cap, (size_t)8));
+    GRID_CK(grid_reserve(&G.d_ctl, &G.ctl_cap, (size_t)12));
     GRID_CK(grid_reserve(&G.d_union, &G.union_cap, (size_t)1));
     GridArgs g; memset(&g, 0, sizeof(g));
     g.tris = d_tris; g.n_tris = n_tris; g.light_pts = d_light_pts; g.n_lights = n_lights;
@@ -963,8 +776,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     g.cell0 = cell0;
     g.lights = G.d_lights; g.lbounds = G.d_lbounds; g.prim_flags = G.d_prim_flags; g.big_list = G.d_big; g.ctl = G.d_ctl; g.uni = G.d_union;
     g.cell_cap = (uint32_t)CELL_CAP;
-    g.no_cover_order = getenv("RTB200_NO_COVER_ORDER") ? 1u : 0u;      // experiment: cells filled in arrival order
-    const unsigned nmax = n_lights > n_tris ? (n_lights > 8 ? n_lights : 8) : (n_tris > 8 ? n_tris : 8);
+    const unsigned nmax = n_lights > n_tris ? (n_lights > 12 ? n_lights : 12) : (n_tris > 12 ? n_tris : 12);
     const unsigned gw = (unsigned)((work + 255) / 256);
     const unsigned gr = (unsigned)((work * RTB_RASTER_SPLIT + 255) / 256);     // k_grid_raster: RTB_RASTER_SPLIT threads per pair
     G.builds++;
@@ -1020,7 +832,8 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     G.spec_ok = false;
     g.speculative = 0u; g.entries_alloc = ENTRY_CAP;
     GRID_CK(cudaEventRecord(G.ev0, st));
-    uint32_t h_ctl[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t h_ctl[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const unsigned long long ENTRY_BUDGET = ENTRY_CAP < (320ull << 20) ? ENTRY_CAP : (320ull << 20);    // list entries one build should stay below
     // A primitive that would cover more than RTB_GRID_MAX_CELLS_PER_PRIM cells of some light's grid goes to the `big` list every
     // ray tests.  That is meant for the ground; in a wide scene (64 bunnies over 1600 x 1400 units) the stretched projections of
     // distant primitives cross the limit by the thousand at the cell size the primitives' own extent suggests.  Coarser cells
@@ -1033,9 +846,12 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
         GRID_CK(cudaGetLastError());
         GRID_CK(cudaMemcpyAsync(h_ctl, G.d_ctl, sizeof(h_ctl), cudaMemcpyDeviceToHost, st));
         GRID_CK(cudaStreamSynchronize(st));
-        if (h_ctl[1] <= RTB_GRID_MAX_BIG || attempt >= 5) break;
-        g.cell0 *= 2.0f;
-        if (dbg) fprintf(stderr, "rtb200 grid: %u big primitives, cells doubled to %g\n", h_ctl[1], g.cell0);
+        unsigned long long est = 0; memcpy(&est, h_ctl + 8, 8);
+        const bool too_big = h_ctl[1] > RTB_GRID_MAX_BIG, too_many = est > ENTRY_BUDGET;
+        if ((!too_big && !too_many) || attempt >= 12) break;
+        // entries fall between 1 / cell (streaks) and 1 / cell^2 (blobs): a modest step, repeated while needed
+        g.cell0 *= too_big ? 2.0f : (est > 4 * ENTRY_BUDGET ? 2.0f : 1.3f);
+        if (dbg) fprintf(stderr, "rtb200 grid: %u big primitives, about %llu entries: cells enlarged to %g\n", h_ctl[1], est, g.cell0);
     }
     G.total_cells = h_ctl[0]; G.n_big = h_ctl[1];
     if (dbg) fprintf(stderr, "rtb200 grid: %u lights, %u cells, %u big primitives (max %u)\n", n_lights, G.total_cells, G.n_big, (unsigned)RTB_GRID_MAX_BIG);

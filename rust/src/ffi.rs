@@ -32,7 +32,6 @@ pub struct RtbSceneOptions {
     pub struct_size: u32, pub shadow_mode: i32, pub primary_mode: i32, pub term_mode: i32,
     pub chunk_rays: u64, pub term_bytes: u64, pub grid_entry_cap: u64,
     pub grid_cell_factor: f32, pub cam_cell_px: f32, pub cdiv_off: i32, pub trace_chunks: i32,
-    pub shadow_kernel: i32, pub primary_kernel: i32,
 }
 
 #[repr(C)]

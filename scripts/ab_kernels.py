@@ -1,5 +1,5 @@
-"""A/B of the kernel forms on the bench frame (gpurun): per-kernel times (RTB_FLAG_PROFILE, chunks in sequence) and the
-overlapped frame time for every (shadow_kernel, primary_kernel) pair, with a CRC of the frame (all must agree).
+"""Kernel times of a bench frame (gpurun): per-kernel times (RTB_FLAG_PROFILE, chunks in sequence) and the overlapped frame
+time, with a CRC of the frame, for a set of scene options (A/B of tunables).
 usage: python scripts/ab_kernels.py [config: 3|3b|4] [extra option=value ...]"""
 import os, sys, zlib
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -18,9 +18,8 @@ else:
     v, c = S.big_bunny(); kw = dict(width=3840, height=2160, nb_ray=16, distance=576.0 if cfg == "3b" else 288.0)
 smp = S.make_samples()
 crcs = set()
-pairs = [tuple(int(x) for x in pr.split(",")) for pr in os.environ.get("AB_PAIRS", "1,1 2,1 1,2 2,2").split()]
-for sk, pk in pairs:
-    sc = rtb200.Scene(v, c, shadow_kernel=sk, primary_kernel=pk, **extra)
+for _ in range(1):
+    sc = rtb200.Scene(v, c, **extra)
     sc.set_samples(smp)
     sc.render(**kw)
     ov, pr, sh, sd = [], [], [], []
@@ -32,7 +31,6 @@ for sk, pk in pairs:
         pr.append(st["primary_ms"]); sh.append(st["shadow_ms"]); sd.append(st["shade_ms"])
     crc = zlib.crc32(img.tobytes()) & 0xffffffff
     crcs.add(crc)
-    print("config %s shadow_kernel %d primary_kernel %d %s: overlapped %.3f ms | primary %.3f shadow %.3f shade %.3f | crc %08x queued %d grid_build %.2f ms"
-          % (cfg, sk, pk, extra, min(ov), np.mean(pr), np.mean(sh), np.mean(sd), crc, st["queued_hits"], st["grid_build_ms"]), flush=True)
+    print("config %s %s: overlapped %.3f ms | primary %.3f shadow %.3f shade %.3f | crc %08x queued %d grid_build %.2f ms"
+          % (cfg, extra, min(ov), np.mean(pr), np.mean(sh), np.mean(sd), crc, st["queued_hits"], st["grid_build_ms"]), flush=True)
     del sc
-print("frames identical:", len(crcs) == 1)

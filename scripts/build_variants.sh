@@ -13,5 +13,5 @@ for spec in "$@"; do
   wait
   nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../variants/librtb200_$name.so build/rtb_api_$name.o build/rtb_trace_$name.o build/rtb_grid_$name.o build/rtb_bvh.o build/rtb_refpair.o build/rtb_peaks.o build/rtb_host.o -cudart shared
   $NV $flags -Xptxas -v -c csrc/rtb_grid.cu -o /dev/null 2> build/rtb_grid_$name.log || true
-  echo "$name: $(grep -A2 'k_shadow_grid2ILb0\|k_primary2ILb0\|k_shadeILb0ELb0' build/rtb_trace_$name.log build/rtb_grid_$name.log | grep -o 'Used [0-9]* registers[^,]*, [0-9]* bytes smem\|Used [0-9]* registers' | tr '\n' ' ')"
+  echo "$name: $(grep -A2 'k_shadow_gridILb0\|k_primaryILb0\|k_shadeILb0ELb0' build/rtb_trace_$name.log build/rtb_grid_$name.log | grep -o 'Used [0-9]* registers[^,]*, [0-9]* bytes smem\|Used [0-9]* registers' | tr '\n' ' ')"
 done

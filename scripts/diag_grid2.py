@@ -1,4 +1,4 @@
-"""Round statistics of k_shadow_grid2 (build with -DRTB_DIAG_GRID=1 -DRTB_NUM_CTRS=32; RTB200_LIB=variants/librtb200_diag2.so)."""
+"""Round statistics of k_shadow_grid (build with -DRTB_DIAG_GRID=1 -DRTB_NUM_CTRS=32; RTB200_LIB=variants/librtb200_diag2.so)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
