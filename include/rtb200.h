@@ -215,6 +215,17 @@ int rtb_render_pixels(rtb_scene* scene, const rtb_render_params* params, const u
  *     (HOST), computed by the same device code the trace kernel's epilogue uses. */
 int rtb_color_to_u8(rtb_scene* scene, const float* linear, uint64_t n, uint8_t* out);
 
+/* --- NO counterpart in the reference: added for callers that cannot allocate (code under
+ *     CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The same conversion as rtb_color_to_u8, by the
+ *     same kernel, but the call allocates NOTHING (no cudaMalloc / cudaFree, no allocating library routine): its device staging --
+ *     which rtb_color_to_u8 cudaMallocs per call -- is a static device array of RTB_COLOR_STATIC_MAX values (5 MiB: 4 input bytes +
+ *     1 output byte per value) that every GPU loading the library holds until the process exits.  n > RTB_COLOR_STATIC_MAX returns
+ *     RTB_ERR_LIMIT.  linear / out are HOST arrays as in rtb_color_to_u8.  Every call on a GPU shares that one array (it keeps the
+ *     previous call's contents; a call overwrites what it reads): calls that overlap on the same GPU -- from several threads or
+ *     scenes -- race and must be serialised by the caller.  Blocking. */
+#define RTB_COLOR_STATIC_MAX (1u << 20)
+int rtb_color_to_u8_static(rtb_scene* scene, const float* linear, uint64_t n, uint8_t* out);
+
 /* Raw device counters of the last render on this scene (16 values; diagnostics of the RTB_FLAG_COUNTERS build, layout in
  * csrc/rtb_common.cuh). */
 int rtb_scene_get_counters(rtb_scene* scene, uint64_t* out16);

@@ -17,6 +17,7 @@ RTB_FLAG_COUNTERS = 1
 RTB_FLAG_PROFILE = 2
 RTB_FLAG_FRAME_ROWS = 4
 RTB_FLAG_GATHER_PEER = 8
+COLOR_STATIC_MAX = 1 << 20
 RTB_TIE_REFERENCE, RTB_TIE_CALLER, RTB_TIE_INDEX = 0, 1, 2
 
 
@@ -71,7 +72,7 @@ class SequenceStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
-EXPORTS = ["rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
+EXPORTS = ["rtb_color_to_u8_static", "rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
            "rtb_render_sequence", "rtb_render_sequence_multi", "rtb_measure_peaks", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render",
            "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj", "rtb_import_obj_ex",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
@@ -104,6 +105,7 @@ def lib():
         L.rtb_render_device.argtypes = [vp, vp, vp, vp]
         L.rtb_render_pixels.argtypes = [vp, vp, vp, C.c_uint64, vp, vp, vp, vp, vp, vp]
         L.rtb_color_to_u8.argtypes = [vp, vp, C.c_uint64, vp]
+        L.rtb_color_to_u8_static.argtypes = [vp, vp, C.c_uint64, vp]
         L.rtb_scene_get_tie_ranks.argtypes = [vp, vp]
         L.rtb_scene_get_nodes.argtypes = [vp, vp]
         L.rtb_scene_get_counters.argtypes = [vp, vp]
@@ -315,6 +317,13 @@ class Scene:
         lin = np.ascontiguousarray(linear, np.float32)
         out = np.zeros(lin.shape, np.uint8)
         _check(lib().rtb_color_to_u8(self._h, _ptr(lin), lin.size, _ptr(out)))
+        return out
+
+    def color_to_u8_static(self, linear):
+        """rtb_color_to_u8_static: the same conversion with no allocation (static device scratch, at most COLOR_STATIC_MAX values)."""
+        lin = np.ascontiguousarray(linear, np.float32)
+        out = np.zeros(lin.shape, np.uint8)
+        _check(lib().rtb_color_to_u8_static(self._h, _ptr(lin), lin.size, _ptr(out)))
         return out
 
     def nodes(self):

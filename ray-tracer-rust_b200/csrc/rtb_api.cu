@@ -32,6 +32,7 @@ cudaError_t rtb_launch_light_groups(const float4*, const float*, uint32_t, uint3
 cudaError_t rtb_launch_deinterleave(const uint8_t*, uint64_t, uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, cudaStream_t);
 cudaError_t rtb_upload_gamma_table(const float*);
 cudaError_t rtb_launch_color_to_u8(const float*, uint64_t, uint8_t*, cudaStream_t);
+cudaError_t rtb_color_to_u8_static_run(int, const float*, uint64_t, uint8_t*, cudaStream_t);
 cudaError_t rtb_launch_get_ranks(const float4*, uint32_t, int*, cudaStream_t);
 cudaError_t rtb_launch_div_selftest(uint64_t, uint64_t, unsigned long long*, cudaStream_t);
 cudaError_t rtb_launch_cdiv_check(float, float, float, uint32_t*, cudaStream_t);
@@ -852,6 +853,18 @@ cleanup:
     cudaFree(d_in); cudaFree(d_out);
     return rc;
 #undef TRY_
+}
+
+// Same result as rtb_color_to_u8 with no allocation of any kind: the staging lives in a static device array (rtb_trace.cu).
+int rtb_color_to_u8_static(rtb_scene* s, const float* linear, uint64_t n, uint8_t* out) {
+    if (!s || (n && (!linear || !out))) return fail(RTB_ERR_ARG, "rtb_color_to_u8_static: null argument");
+    if (n > RTB_COLOR_STATIC_MAX)
+        return fail(RTB_ERR_LIMIT, "rtb_color_to_u8_static: %llu values exceed the static scratch of %u values per call (use rtb_color_to_u8, or split the call)",
+                    (unsigned long long)n, (unsigned)RTB_COLOR_STATIC_MAX);
+    if (n == 0) return RTB_OK;
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(rtb_color_to_u8_static_run(s->device, linear, n, out, s->stream));
+    return RTB_OK;
 }
 
 int rtb_scene_get_nodes(rtb_scene* s, float* out) {

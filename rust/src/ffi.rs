@@ -9,6 +9,7 @@ pub const RTB_FLAG_COUNTERS: u32 = 1;
 pub const RTB_FLAG_PROFILE: u32 = 2;
 pub const RTB_FLAG_FRAME_ROWS: u32 = 4;
 pub const RTB_FLAG_GATHER_PEER: u32 = 8;
+pub const RTB_COLOR_STATIC_MAX: u64 = 1 << 20;
 pub const RTB_TIE_REFERENCE: u32 = 0;
 pub const RTB_TIE_CALLER: u32 = 1;
 pub const RTB_TIE_INDEX: u32 = 2;
@@ -96,6 +97,7 @@ extern "C" {
                              rgb_lin: *mut f32, rgb8: *mut u8, hit_count: *mut u8, prim0: *mut i32, t0: *mut f32,
                              stats: *mut RtbStats) -> i32;
     pub fn rtb_color_to_u8(scene: *mut RtbScene, linear: *const f32, n: u64, out: *mut u8) -> i32;
+    pub fn rtb_color_to_u8_static(scene: *mut RtbScene, linear: *const f32, n: u64, out: *mut u8) -> i32;
     pub fn rtb_scene_get_counters(scene: *mut RtbScene, out16: *mut u64) -> i32;
     pub fn rtb_selftest_division(scene: *mut RtbScene, seed: u64, n: u64, mismatches: *mut u64) -> i32;
     pub fn rtb_scene_get_tie_ranks(scene: *mut RtbScene, out: *mut i32) -> i32;
