@@ -16,6 +16,6 @@ except Exception as e:
     print("  no line:", e)
 PY
 }
-run 3 8; run 3 4; run 4 8; run 5 8; run 3b 8
+run 3 8; run 3 4; run 3 2; run 4 8; run 5 8; run 3b 8
 timeout 300 ./ray-tracer-rust_b200/rt_main assets/models/big_bunny.obj --gpus 8 --width 3840 --height 2160 --spp 16 --out gpurun_out/rt_main_8gpu.png
 timeout 300 ./ray-tracer-rust_b200/rt_main assets/models/big_bunny.obj --gpus 8 --orbit 120 --out /tmp/orb.png | tail -1
