@@ -114,7 +114,7 @@ def cpu_baseline_sample(cfg, n_threads=0, target_pixels=None):
     threads = n_threads if n_threads > 0 else max(1, (os.cpu_count() or 2) - 1)
     per_thread = 1500 if cfg["nb_ray"] == 16 else 20000        # ~120 pixels/s/thread at 16 spp x 100 light samples -> ~12 s
     if big:
-        per_thread = 6                                          # brute force: ~0.3 pixels/s/thread on the ground rows
+        per_thread = 200                                        # brute force over 317 953 primitives: ~12 pixels/s/thread -> ~17 s
     n_pix = target_pixels or per_thread * threads
     rng = np.random.default_rng(12345)
     pix = np.stack([rng.integers(0, cfg["width"], n_pix), rng.integers(0, cfg["height"], n_pix)], 1).astype(np.uint32)
