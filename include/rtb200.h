@@ -39,7 +39,8 @@ typedef struct rtb_scene rtb_scene;
 typedef struct {
     uint32_t n_tris;          /* primitives in the reference's order: OBJ faces in argv order, ground last */
     const float* verts;       /* n_tris * 9: v0.xyz v1.xyz v2.xyz (Triangle::new args, triangle.rs:22) */
-    const float* colors;      /* n_tris * 3: linear RGB (Color, color.rs:4-8) */
+    const float* colors;      /* n_tris * 3: linear RGB (Color, color.rs:4-8); NULL: every primitive white, as import_obj makes them
+                                 (src/main.rs:143) -- saves the 12 bytes per triangle of host array and upload for large meshes */
     const int32_t* tie_rank;  /* optional n_tris: order used ONLY to break exact-equal-distance ties between two
                                  primitives (larger wins; the reference's rule is "later leaf in its tree",
                                  bounding_volume_hierarchy.rs:123-130).  NULL: computed on the device by
@@ -278,6 +279,23 @@ void rtb_free(void* p);
  * equal rtb_import_obj's. */
 #define RTB_OBJ_MTL 1u
 int rtb_import_obj_ex(const char* path, uint32_t flags, float** verts_out, float** kd_out, float** ks_ns_out, uint32_t* n_out);
+
+/* import_obj (src/main.rs:114-149) for large files: rtb_import_obj_ex's grammar without materials, parsed by n_threads
+ * host threads (0 = all cores) in three passes over chunks of the file (count, vertices, faces) straight into one output array.
+ * flags & RTB_OBJ_PINNED: *verts_out is page-locked host memory (cudaHostAlloc: rtb_scene_create then uploads it as one DMA) and is
+ * freed with rtb_free_pinned; otherwise malloc'ed, rtb_free.  The triangles equal rtb_import_obj_ex's, in the same order.
+ * stats may be NULL.  An unreadable path returns RTB_ERR_IO with "Not a valid path: ..." as rtb_import_obj does. */
+#define RTB_OBJ_PINNED 2u
+typedef struct {
+    double read_s, parse_s;          /* wall time of reading the file into memory / of the three passes (without alloc_s) */
+    double alloc_s;                  /* time inside the output allocation: page-locking costs about 1.5 s per GB (cudaHostAlloc), which only
+                                        pays when the array is uploaded several times (one scene per GPU); a single upload from pageable
+                                        memory is faster than pinning first */
+    uint64_t file_bytes;
+    uint32_t threads, n_vertices;
+} rtb_import_stats;
+int rtb_import_obj_parallel(const char* path, uint32_t n_threads, uint32_t flags, float** verts_out, uint32_t* n_out, rtb_import_stats* stats);
+void rtb_free_pinned(void* p);
 
 /* Deterministic stand-in for thread_rng (src/main.rs:260-265): SplitMix64(seed) stream, value j =
  * top 24 bits * 2^-24; out holds 2*n_pairs floats. */

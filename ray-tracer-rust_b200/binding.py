@@ -60,6 +60,11 @@ class SceneOptions(C.Structure):
                 ("grid_cell_factor", C.c_float), ("cam_cell_px", C.c_float), ("cdiv_off", C.c_int32), ("trace_chunks", C.c_int32)]
 
 
+class ImportStats(C.Structure):
+    _fields_ = [("read_s", C.c_double), ("parse_s", C.c_double), ("alloc_s", C.c_double), ("file_bytes", C.c_uint64), ("threads", C.c_uint32),
+                ("n_vertices", C.c_uint32)]
+
+
 class CameraPose(C.Structure):
     _fields_ = [("eye", C.c_float * 3), ("look_at", C.c_float * 3), ("up", C.c_float * 3), ("distance", C.c_float)]
 
@@ -72,7 +77,7 @@ class SequenceStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
-EXPORTS = ["rtb_color_to_u8_static", "rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
+EXPORTS = ["rtb_import_obj_parallel", "rtb_free_pinned", "rtb_color_to_u8_static", "rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
            "rtb_render_sequence", "rtb_render_sequence_multi", "rtb_measure_peaks", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render",
            "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj", "rtb_import_obj_ex",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
@@ -118,6 +123,8 @@ def lib():
         L.rtb_import_obj.argtypes = [C.c_char_p, vp, vp]
         L.rtb_import_obj_ex.argtypes = [C.c_char_p, C.c_uint32, vp, vp, vp, vp]
         L.rtb_free.argtypes = [vp]; L.rtb_free.restype = None
+        L.rtb_free_pinned.argtypes = [vp]; L.rtb_free_pinned.restype = None
+        L.rtb_import_obj_parallel.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, vp, vp, vp]
         L.rtb_fill_samples.argtypes = [C.c_uint64, C.c_uint32, vp]; L.rtb_fill_samples.restype = None
         L.rtb_write_png.argtypes = [C.c_char_p, vp, C.c_uint32, C.c_uint32]
         L.rtb_last_error.restype = C.c_char_p
@@ -172,6 +179,44 @@ def import_obj_ex(path, mtl=True):
     return tuple(out)
 
 
+RTB_OBJ_PINNED = 2
+
+
+class _HostArrayOwner:
+    """Keeps a library-allocated host array alive for the numpy view over it; frees it with the matching call."""
+
+    def __init__(self, ptr, pinned):
+        self.ptr, self.pinned = ptr, pinned
+
+    def __del__(self):
+        if self.ptr:
+            (lib().rtb_free_pinned if self.pinned else lib().rtb_free)(self.ptr)
+            self.ptr = None
+
+
+def import_obj_parallel(path, n_threads=0, pinned=False):
+    """rtb_import_obj_parallel -> ((n, 9) float32 view of the library's array (page-locked if pinned), stats dict).
+    The view keeps the allocation alive; it is freed when the last reference to the array goes."""
+    verts = C.c_void_p()
+    n = C.c_uint32(0)
+    st = ImportStats()
+    _check(lib().rtb_import_obj_parallel(os.fsencode(path), n_threads, RTB_OBJ_PINNED if pinned else 0, C.byref(verts), C.byref(n), C.byref(st)))
+    stats = {k: getattr(st, k) for k, _ in ImportStats._fields_}
+    if n.value == 0:
+        return np.zeros((0, 9), np.float32), stats
+    owner = _HostArrayOwner(verts.value, pinned)
+    buf = (C.c_float * (n.value * 9)).from_address(verts.value)
+    arr = np.frombuffer(buf, dtype=np.float32).reshape(n.value, 9)
+    arr = arr.view(_OwnedArray)
+    arr._owner = owner
+    return arr, stats
+
+
+class _OwnedArray(np.ndarray):
+    """ndarray that carries a reference to the owner of its memory (views of it keep it through .base)."""
+    _owner = None
+
+
 def create_ground():
     """create_ground (src/main.rs:102-111): one grey triangle."""
     return (np.array([[-10000.0, 0.0, -10000.0, 10000.0, 0.0, -10000.0, 0.0, 0.0, 10000.0]], np.float32),
@@ -215,13 +260,13 @@ class Scene:
 
     def __init__(self, verts, colors, light=DEFAULT_LIGHT, device=0, tie_rank=None, **options):
         self.verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
-        self.colors = np.ascontiguousarray(colors, np.float32).reshape(-1, 3)
-        if self.verts.shape[0] != self.colors.shape[0]:
+        self.colors = None if colors is None else np.ascontiguousarray(colors, np.float32).reshape(-1, 3)   # None: all white (src/main.rs:143)
+        if self.colors is not None and self.verts.shape[0] != self.colors.shape[0]:
             raise ValueError("verts/colors length mismatch")
         d = SceneDesc()
         d.n_tris = self.verts.shape[0]
         d.verts = self.verts.ctypes.data if d.n_tris else None
-        d.colors = self.colors.ctypes.data if d.n_tris else None
+        d.colors = self.colors.ctypes.data if (d.n_tris and self.colors is not None) else None
         self._rank = None if tie_rank is None else np.ascontiguousarray(tie_rank, np.int32)
         d.tie_rank = self._rank.ctypes.data if self._rank is not None else None
         d.light[:] = [float(x) for x in np.asarray(light, np.float32).reshape(9)]

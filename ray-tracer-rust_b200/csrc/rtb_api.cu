@@ -29,6 +29,7 @@ cudaError_t rtb_grid_validate(RtbGrid&, cudaStream_t, bool*);
 void rtb_grid_free(RtbGrid&);
 cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, float*, cudaStream_t);
 cudaError_t rtb_launch_light_groups(const float4*, const float*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint16_t*, float*, cudaStream_t);
+cudaError_t rtb_launch_fill_f32(float*, size_t, float, cudaStream_t);
 cudaError_t rtb_launch_deinterleave(const uint8_t*, uint64_t, uint8_t*, uint32_t, uint32_t, uint32_t, uint32_t, cudaStream_t);
 cudaError_t rtb_upload_gamma_table(const float*);
 cudaError_t rtb_launch_color_to_u8(const float*, uint64_t, uint8_t*, cudaStream_t);
@@ -203,7 +204,7 @@ int rtb_scene_create_ex(const rtb_scene_desc* desc, const rtb_scene_options* opt
         memcpy(&opt, opt_in, opt_in->struct_size);
     }
     *out = nullptr;
-    if (desc->n_tris && (!desc->verts || !desc->colors)) return fail(RTB_ERR_ARG, "rtb_scene_create: null vertex/colour array");
+    if (desc->n_tris && !desc->verts) return fail(RTB_ERR_ARG, "rtb_scene_create: null vertex array");
     if (desc->n_tris > 0x3fffffffu) return fail(RTB_ERR_LIMIT, "rtb_scene_create: too many primitives");
     int n_dev = 0;
     CUDA_TRY(cudaGetDeviceCount(&n_dev));
@@ -239,7 +240,7 @@ int rtb_scene_create_ex(const rtb_scene_desc* desc, const rtb_scene_options* opt
     if (const char* env = getenv("RTB200_TERM_MB")) { const long long v = atoll(env); if (v >= 0) s->term_bytes = (uint64_t)v << 20; }
     s->grid.entry_cap_limit = opt.grid_entry_cap; s->cam_grid.entry_cap_limit = opt.grid_entry_cap;
     s->all_grey = true;
-    for (uint32_t i = 0; i < desc->n_tris && s->all_grey; ++i)
+    for (uint32_t i = 0; desc->colors && i < desc->n_tris && s->all_grey; ++i)
         s->all_grey = desc->colors[3 * i] == desc->colors[3 * i + 1] && desc->colors[3 * i + 1] == desc->colors[3 * i + 2];
     s->trace_chunks = opt.trace_chunks != 0;
     if (const char* env = getenv("RTB200_TRACE_CHUNKS")) s->trace_chunks = atoi(env) != 0;
@@ -263,7 +264,8 @@ int rtb_scene_create_ex(const rtb_scene_desc* desc, const rtb_scene_options* opt
     if (n) {
         TRY_(cudaMalloc(&d_verts, (size_t)n * 9 * 4)); TRY_(cudaMalloc(&d_colors, (size_t)n * 3 * 4));
         TRY_(cudaMemcpyAsync(d_verts, desc->verts, (size_t)n * 9 * 4, cudaMemcpyHostToDevice, s->stream));
-        TRY_(cudaMemcpyAsync(d_colors, desc->colors, (size_t)n * 3 * 4, cudaMemcpyHostToDevice, s->stream));
+        if (desc->colors) TRY_(cudaMemcpyAsync(d_colors, desc->colors, (size_t)n * 3 * 4, cudaMemcpyHostToDevice, s->stream));
+        else TRY_(rtb_launch_fill_f32(d_colors, (size_t)n * 3, 1.0f, s->stream));                 // Color(1, 1, 1), src/main.rs:143
         if (desc->tie_rank) {
             TRY_(cudaMalloc(&d_rank, (size_t)n * 4));
             TRY_(cudaMemcpyAsync(d_rank, desc->tie_rank, (size_t)n * 4, cudaMemcpyHostToDevice, s->stream));
@@ -925,6 +927,27 @@ int rtb_deinterleave_bands(int32_t device, const void* d_staged, uint64_t stride
 }
 
 }  // extern "C"
+
+// ---- parallel OBJ import into (optionally) pinned memory: the parser is host/rtb_obj_parallel.cpp, the allocator lives here -------
+int rtb_obj_parallel_core(const char*, uint32_t, void* (*)(size_t), float**, uint32_t*, rtb_import_stats*, std::string*);
+static void* alloc_pinned_(size_t bytes) { void* p = nullptr; return cudaHostAlloc(&p, bytes, cudaHostAllocDefault) == cudaSuccess ? p : nullptr; }
+static void* alloc_pageable_(size_t bytes) { return malloc(bytes); }
+
+extern "C" int rtb_import_obj_parallel(const char* path, uint32_t n_threads, uint32_t flags, float** verts_out, uint32_t* n_out, rtb_import_stats* stats) {
+    if (!path || !verts_out || !n_out) return fail(RTB_ERR_ARG, "rtb_import_obj_parallel: null argument");
+    if (stats) memset(stats, 0, sizeof(*stats));
+    std::string err;
+    const bool pinned = (flags & RTB_OBJ_PINNED) != 0;
+    const int rc = rtb_obj_parallel_core(path, n_threads, pinned ? alloc_pinned_ : alloc_pageable_, verts_out, n_out, stats, &err);
+    if (rc != RTB_OK) {
+        if (*verts_out) { if (pinned) cudaFreeHost(*verts_out); else free(*verts_out); }
+        *verts_out = nullptr; *n_out = 0;
+        if (pinned) cudaGetLastError();
+        return fail(rc, "%s", err.c_str());
+    }
+    return RTB_OK;
+}
+extern "C" void rtb_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
 // ---- several GPUs behind one call ---------------------------------------------------------------------------------------------
 // One host thread per device (the reference's render() fans out to its own worker threads and joins them, src/main.rs:269-303).

@@ -33,13 +33,20 @@ fn main() {
         assert!(ok, "nvcc failed on {}", src.display());
         objs.push(obj);
     }
-    let host = out.join("rtb_host.o");
-    let ok = Command::new("g++")
-        .args(["-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-c"])
-        .arg(pkg.join("host").join("rtb_host.cpp")).arg("-o").arg(&host)
-        .status().expect("g++ not found").success();
-    assert!(ok);
-    objs.push(host);
+    // every host/rtb_*.cpp (plain C++: OBJ readers, sample table, PNG writer), as `HOST_SRCS := $(wildcard host/rtb_*.cpp)` in the Makefile
+    let mut hosts: Vec<std::path::PathBuf> = std::fs::read_dir(pkg.join("host")).expect("host/ missing")
+        .filter_map(|e| e.ok()).map(|e| e.path())
+        .filter(|p| p.extension().map_or(false, |x| x == "cpp") && p.file_name().unwrap().to_string_lossy().starts_with("rtb_")).collect();
+    hosts.sort();
+    for src in hosts {
+        let obj = out.join(format!("{}.o", src.file_stem().unwrap().to_string_lossy()));
+        let ok = Command::new("g++")
+            .args(["-O2", "-std=c++17", "-fPIC", "-ffp-contract=off", "-pthread", "-c"])
+            .arg(&src).arg("-o").arg(&obj)
+            .status().expect("g++ not found").success();
+        assert!(ok);
+        objs.push(obj);
+    }
     let ok = Command::new(&nvcc).args(arch).args(["-shared", "-cudart", "shared", "-o"])
         .arg(out.join("librtb200.so")).args(&objs)
         .status().unwrap().success();

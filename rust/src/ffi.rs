@@ -9,6 +9,8 @@ pub const RTB_FLAG_COUNTERS: u32 = 1;
 pub const RTB_FLAG_PROFILE: u32 = 2;
 pub const RTB_FLAG_FRAME_ROWS: u32 = 4;
 pub const RTB_FLAG_GATHER_PEER: u32 = 8;
+pub const RTB_OBJ_MTL: u32 = 1;
+pub const RTB_OBJ_PINNED: u32 = 2;
 pub const RTB_COLOR_STATIC_MAX: u64 = 1 << 20;
 pub const RTB_TIE_REFERENCE: u32 = 0;
 pub const RTB_TIE_CALLER: u32 = 1;
@@ -38,6 +40,10 @@ pub struct RtbSceneOptions {
 #[repr(C)]
 #[derive(Clone, Copy)]
 pub struct RtbCameraPose { pub eye: [f32; 3], pub look_at: [f32; 3], pub up: [f32; 3], pub distance: f32 }
+
+#[repr(C)]
+#[derive(Default)]
+pub struct RtbImportStats { pub read_s: f64, pub parse_s: f64, pub alloc_s: f64, pub file_bytes: u64, pub threads: u32, pub n_vertices: u32 }
 
 #[repr(C)]
 #[derive(Default)]
@@ -111,6 +117,9 @@ extern "C" {
     pub fn rtb_import_obj(path: *const c_char, verts_out: *mut *mut f32, n_out: *mut u32) -> i32;
     pub fn rtb_import_obj_ex(path: *const c_char, flags: u32, verts_out: *mut *mut f32, kd_out: *mut *mut f32,
                              ks_ns_out: *mut *mut f32, n_out: *mut u32) -> i32;
+    pub fn rtb_import_obj_parallel(path: *const c_char, n_threads: u32, flags: u32, verts_out: *mut *mut f32, n_out: *mut u32,
+                                   stats: *mut RtbImportStats) -> i32;
+    pub fn rtb_free_pinned(p: *mut c_void);
     pub fn rtb_free(p: *mut c_void);
     pub fn rtb_fill_samples(seed: u64, n_pairs: u32, out: *mut f32);
     pub fn rtb_write_png(path: *const c_char, rgb8: *const u8, width: u32, height: u32) -> i32;

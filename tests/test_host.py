@@ -36,7 +36,8 @@ def test_struct_layouts_match_header(rtb, tmp_path):
     import subprocess
     B = rtb.binding
     pairs = [("rtb_scene_desc", B.SceneDesc), ("rtb_render_params", B.RenderParams), ("rtb_stats", B.Stats), ("rtb_scene_info", B.SceneInfo),
-             ("rtb_scene_options", B.SceneOptions), ("rtb_camera_pose", B.CameraPose), ("rtb_sequence_stats", B.SequenceStats)]
+             ("rtb_scene_options", B.SceneOptions), ("rtb_camera_pose", B.CameraPose), ("rtb_sequence_stats", B.SequenceStats),
+             ("rtb_import_stats", B.ImportStats)]
     src = ['#include <stdio.h>', '#include <stddef.h>', '#include "rtb200.h"', 'int main(void) {']
     for cname, ct in pairs:
         src.append('printf("%s %%zu", sizeof(%s));' % (cname, cname))
@@ -54,7 +55,8 @@ def test_struct_layouts_match_header(rtb, tmp_path):
     # the Rust mirror: same field names in the same order
     ffi = open(os.path.join(ROOT, "rust", "src", "ffi.rs")).read()
     for rname, ct in (("RtbSceneDesc", B.SceneDesc), ("RtbRenderParams", B.RenderParams), ("RtbStats", B.Stats), ("RtbSceneInfo", B.SceneInfo),
-                      ("RtbSceneOptions", B.SceneOptions), ("RtbCameraPose", B.CameraPose), ("RtbSequenceStats", B.SequenceStats)):
+                      ("RtbSceneOptions", B.SceneOptions), ("RtbCameraPose", B.CameraPose), ("RtbSequenceStats", B.SequenceStats),
+                      ("RtbImportStats", B.ImportStats)):
         body = re.search(r"pub struct %s \{(.*?)\n?\}" % rname, ffi, re.S).group(1)
         assert re.findall(r"pub (\w+):", body) == [f for f, _ in ct._fields_], rname
 
@@ -68,8 +70,9 @@ def test_rust_build_uses_the_makefile_sources():
     build_rs = open(os.path.join(ROOT, "rust", "build.rs")).read()
     mk = open(os.path.join(ROOT, "ray-tracer-rust_b200", "Makefile")).read()
     assert "read_dir" in build_rs and '"cu"' in build_rs and "$(wildcard csrc/*.cu)" in mk
+    assert '"cpp"' in build_rs and 'starts_with("rtb_")' in build_rs and "$(wildcard host/rtb_*.cpp)" in mk     # the plain C++ host files, same rule
     for name in cu:
-        assert name not in build_rs.replace("rtb_host", ""), name       # no hard-coded list
+        assert name not in build_rs, name                               # no hard-coded list
         assert ("build/%s.o" % name) not in mk, name
     # same compiler flags where they matter for the arithmetic
     for flag in ("-fmad=false", "arch=compute_100a,code=sm_100a", "-ffp-contract=off", "-lineinfo"):
@@ -237,3 +240,44 @@ def test_reciprocal_integer_division_rule():
         fix = r >= d
         q = q + fix.astype(np.uint64); r = r - d * fix.astype(np.uint64)
         assert (q == ns // d).all() and (r == ns % d).all(), int(d)
+
+
+def test_import_obj_parallel_equals_the_serial_readers(rtb, tmp_path):
+    """the multi-threaded reader gives rtb_import_obj_ex's triangles in the same order, for any thread count, on the
+    shipped models, on the robust-syntax cases, and on a file large enough for every chunk boundary to fall inside the data."""
+    import subprocess
+    for name in ("big_bunny.obj", "bunny.obj"):
+        path = os.path.join(S.MODELS, name)
+        want = rtb.import_obj_ex(path, mtl=False)[0]
+        assert (want == S.parse_obj(path)).all()
+        for t in (1, 2, 3, 7, 16):
+            got, st = rtb.import_obj_parallel(path, n_threads=t)
+            assert got.shape == want.shape and (got.view(np.uint32) == want.view(np.uint32)).all(), (name, t)
+            assert st["file_bytes"] == os.path.getsize(path) and st["n_vertices"] == 2503
+    p = tmp_path / "robust.obj"
+    p.write_bytes(b"# comment\r\nmtllib nothing.mtl\r\nv  0 0 0\r\nv\t1 0 0 1.0\nv 0 1 0\nv 1 1 0 # trailing\n\nusemtl x\nf 1/1/1 2/2/2 3/3/3\n"
+                  b"f -1 -2 -3\nf 1//1 2//2 4//4 3//3\nv +2.5e0 1e-3 -0.0\nf 1 2 -1\ns off\n")
+    want = rtb.import_obj_ex(str(p), mtl=False)[0]
+    assert len(want) == 5
+    for t in (1, 2, 4):
+        got, _ = rtb.import_obj_parallel(str(p), n_threads=t)
+        assert (got.view(np.uint32) == want.view(np.uint32)).all(), t
+    # errors: the same messages as the serial reader, with the right line number from any chunk
+    bad = tmp_path / "bad.obj"
+    bad.write_text("v 0 0 0\n" * 3000 + "v 1 x 0\n" + "f 1 2 3\n" * 10)
+    with pytest.raises(rtb.RtbError, match="malformed vertex at line 3001"):
+        rtb.import_obj_parallel(str(bad), n_threads=5)
+    bad.write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\n" + "f 1 2 3\n" * 4000 + "f 1 2 9\n")
+    with pytest.raises(rtb.RtbError, match="malformed face at line 4004"):
+        rtb.import_obj_parallel(str(bad), n_threads=6)
+    with pytest.raises(rtb.RtbError, match="Not a valid path"):
+        rtb.import_obj_parallel(str(tmp_path / "missing.obj"))
+    # 3 x 3 flattened copies written by the instancing tool == the numpy construction of SURVEY 8d config 4
+    tool = os.path.join(ROOT, "ray-tracer-rust_b200", "obj_instances")
+    if not os.path.exists(tool):
+        subprocess.check_call(["make", "-C", os.path.dirname(tool), "obj_instances"], stdout=subprocess.DEVNULL)
+    out = tmp_path / "inst.obj"
+    subprocess.check_call([tool, os.path.join(S.MODELS, "big_bunny.obj"), str(out), "3"], stdout=subprocess.DEVNULL)
+    got, st = rtb.import_obj_parallel(str(out), n_threads=8)
+    want = S.instanced_bunnies(3)[0][:-1]
+    assert got.shape == want.shape and (got.view(np.uint32) == want.view(np.uint32)).all()
