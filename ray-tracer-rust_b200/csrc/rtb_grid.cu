@@ -259,35 +259,65 @@ __global__ void k_grid_sat_cols(uint32_t* __restrict__ sat, const GridUnion* __r
 
 // ---- passes C / D: conservative rasterisation of every projected primitive into its light point's grid -----------------
 // FILL = false: count per cell (cell_fill);  FILL = true: write the primitive at cell_start[cell] + cursor.
-#ifndef RTB_RASTER_SPLIT
-#define RTB_RASTER_SPLIT 1
-#endif
+// Work is dealt to the lanes of a warp twice, because both levels are ragged (a projection covers 1 to 2 048 rows, a row span 1 to
+// thousands of cells; a thread that walked its own rows and spans left two thirds of its warp idle -- ncu: 10 of 32 threads active,
+// 13 warp instructions per listed cell):
+//   1. every thread sets up ONE (light point, primitive) pair -- projection, clipped-edge coefficients, row range -- and leaves the
+//      record in shared memory;
+//   2. the rows of the warp's 32 pairs are concatenated (exclusive scan of the row counts; the owner of item j is found by a
+//      five-step search over the lanes' offsets) and lane j of a round computes the cell span [sx0, sx1] of row item j;
+//   3. the cells of the round's 32 spans are concatenated the same way and lane j of an emission round lists cell j.  The fill pass
+//      needs the position an atomic returns: four emission rounds are issued together (offsets loaded, atomics issued, then the
+//      stores), or the pass is one long chain of L2 round trips per warp.
+#define RTB_RASTER_REC 17
 template <bool FILL>
-__global__ void k_grid_raster(GridArgs g) {
-    // RTB_RASTER_SPLIT threads share one (light point, primitive) pair, rows dealt round-robin: the fill pass waits for the position
-    // every atomic returns, so shorter per-thread chains (and more of them in flight) are what makes it faster
-    const uint64_t tt = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const uint64_t t = tt / RTB_RASTER_SPLIT;
-    const int sub = (int)(tt - t * RTB_RASTER_SPLIT);
-    uint32_t mine = 0;                                            // cells this thread listed its primitive in (count pass)
+__global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
+    __shared__ float rec[RTB_RASTER_REC][256];                    // [field][thread]: lanes read distinct owners -> distinct banks
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u, wbase = threadIdx.x & ~31u;
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t mine = 0;                                            // cells this thread listed (count pass)
     bool work = t < (uint64_t)g.n_lights * g.n_tris;
     const uint32_t light = work ? (uint32_t)(t / g.n_tris) : 0u, prim = work ? (uint32_t)(t - (uint64_t)light * g.n_tris) : 0u;
     work = work && !g.prim_flags[prim];
-    GridLight G = g.lights[light];
-    work = work && G.nx > 0 && G.nz > 0;
-    float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0, q2 = q0;
-    if (work) { q0 = g.tris[3 * prim]; q1 = g.tris[3 * prim + 1]; q2 = g.tris[3 * prim + 2]; }
-    float x[3] = {0.f, 0.f, 0.f}, z[3] = {0.f, 0.f, 0.f};
-    work = work && grid_project(G.px, G.py, G.pz, G.H, mk3(q0.x, q0.y, q0.z), x[0], z[0]) &&
-           grid_project(G.px, G.py, G.pz, G.H, mk3(q1.x, q1.y, q1.z), x[1], z[1]) &&
-           grid_project(G.px, G.py, G.pz, G.H, mk3(q2.x, q2.y, q2.z), x[2], z[2]);     // (always true here: such a primitive is flagged)
-    if (work) {
-    const float bx0 = fminf(fminf(x[0], x[1]), x[2]), bx1 = fmaxf(fmaxf(x[0], x[1]), x[2]);
-    const float bz0 = fminf(fminf(z[0], z[1]), z[2]), bz1 = fmaxf(fmaxf(z[0], z[1]), z[2]);
-    const float m = grid_margin(G.cell, fmaxf(fmaxf(fabsf(bx0), fabsf(bx1)), fmaxf(fabsf(bz0), fabsf(bz1))), G.px, G.pz, G.H);
-    int cx0 = (int)floorf((bx0 - m - G.x0) * G.inv_cell), cx1 = (int)floorf((bx1 + m - G.x0) * G.inv_cell);
-    int cz0 = (int)floorf((bz0 - m - G.z0) * G.inv_cell), cz1 = (int)floorf((bz1 + m - G.z0) * G.inv_cell);
-    cx0 = max(cx0, 0); cz0 = max(cz0, 0); cx1 = min(cx1, G.nx - 1); cz1 = min(cz1, G.nz - 1);
+    int n_rows = 0;
+    {
+        const GridLight G = g.lights[light];
+        work = work && G.nx > 0 && G.nz > 0;
+        float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0, q2 = q0;
+        if (work) { q0 = g.tris[3 * prim]; q1 = g.tris[3 * prim + 1]; q2 = g.tris[3 * prim + 2]; }
+        float x[3] = {0.f, 0.f, 0.f}, z[3] = {0.f, 0.f, 0.f};
+        work = work && grid_project(G.px, G.py, G.pz, G.H, mk3(q0.x, q0.y, q0.z), x[0], z[0]) &&
+               grid_project(G.px, G.py, G.pz, G.H, mk3(q1.x, q1.y, q1.z), x[1], z[1]) &&
+               grid_project(G.px, G.py, G.pz, G.H, mk3(q2.x, q2.y, q2.z), x[2], z[2]);     // (always true here: such a primitive is flagged)
+        if (work) {
+            const float bx0 = fminf(fminf(x[0], x[1]), x[2]), bx1 = fmaxf(fmaxf(x[0], x[1]), x[2]);
+            const float bz0 = fminf(fminf(z[0], z[1]), z[2]), bz1 = fmaxf(fmaxf(z[0], z[1]), z[2]);
+            const float m = grid_margin(G.cell, fmaxf(fmaxf(fabsf(bx0), fabsf(bx1)), fmaxf(fabsf(bz0), fabsf(bz1))), G.px, G.pz, G.H);
+            int cx0 = (int)floorf((bx0 - m - G.x0) * G.inv_cell), cx1 = (int)floorf((bx1 + m - G.x0) * G.inv_cell);
+            int cz0 = (int)floorf((bz0 - m - G.z0) * G.inv_cell), cz1 = (int)floorf((bz1 + m - G.z0) * G.inv_cell);
+            cx0 = max(cx0, 0); cz0 = max(cz0, 0); cx1 = min(cx1, G.nx - 1); cz1 = min(cz1, G.nz - 1);
+            n_rows = max(cz1 - cz0 + 1, 0);
+            float ext = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int k1 = (k + 1) % 3;
+                const float dz = z[k1] - z[k];
+                rec[k][threadIdx.x] = x[k]; rec[3 + k][threadIdx.x] = z[k]; rec[6 + k][threadIdx.x] = x[k1] - x[k];
+                rec[9 + k][threadIdx.x] = dz != 0.0f ? 1.0f / dz : 0.0f;                    // 0: a horizontal edge
+                ext = fmaxf(ext, fmaxf(fabsf(x[k]), fabsf(z[k])));
+            }
+            rec[12][threadIdx.x] = m;
+            rec[13][threadIdx.x] = 8e-6f * (ext + (bx1 - bx0) + (bz1 - bz0)) + 1e-30f;     // eps
+            rec[14][threadIdx.x] = __int_as_float(cx0); rec[15][threadIdx.x] = __int_as_float(cx1); rec[16][threadIdx.x] = __int_as_float(cz0);
+        }
+    }
+    __syncwarp();
+    int incl_r = n_rows;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl_r, d); if ((int)lane >= d) incl_r += v; }
+    const int excl_r = incl_r - n_rows, R = __shfl_sync(FULL, incl_r, 31);
+    const float inf = __int_as_float(0x7f800000);
     // Scan conversion by rows.  A cell belongs to the primitive iff its m-dilated rectangle meets the projected triangle.  For the
     // row cz that is a statement about x alone: the part of the (convex) triangle inside the dilated slab Z0 <= z <= Z1 projects
     // onto an x interval [X0, X1] -- the extreme x of the three edges clipped to the slab -- and the cells of the row whose dilated
@@ -295,66 +325,119 @@ __global__ void k_grid_raster(GridArgs g) {
     // three edge functions per CELL of the bounding box, and no cells beyond the triangle's corners.  Rounding (parameters in [0, 1]
     // to 2^-22, x to a few ulps) is covered by `eps`, itself far below the margin m that makes the rasterisation conservative.
     // FILL also finds the cells the triangle covers entirely (both z edges of the dilated rectangle inside it) for the ordering below.
-    float xa[3], za[3], dx[3], dz[3], idz[3];
-    float ext = 0.0f;
+    for (int rb = 0; rb < R; rb += 32) {
+        const int ri = rb + (int)lane;
+        int own = 0, own_ex = 0;                                  // the last lane whose offset is <= ri (it has rows)
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int k1 = (k + 1) % 3;
-        xa[k] = x[k]; za[k] = z[k]; dx[k] = x[k1] - x[k]; dz[k] = z[k1] - z[k];
-        idz[k] = dz[k] != 0.0f ? 1.0f / dz[k] : 0.0f;
-        ext = fmaxf(ext, fmaxf(fabsf(x[k]), fabsf(z[k])));
-    }
-    const float eps = 8e-6f * (ext + (bx1 - bx0) + (bz1 - bz0)) + 1e-30f;
-    const float inf = __int_as_float(0x7f800000);
-    for (int cz = cz0 + sub; cz <= cz1; cz += RTB_RASTER_SPLIT) {
-        const float Z0 = G.z0 + cz * G.cell - m - eps, Z1 = G.z0 + (cz + 1) * G.cell + m + eps;
-        float X0 = inf, X1 = -inf;                               // x range of the triangle within the slab
-        float i0lo = inf, i0hi = -inf, i1lo = inf, i1hi = -inf;  // x range of the triangle AT z = Z0 and AT z = Z1 (FILL)
+        for (int step = 16; step >= 1; step >>= 1) {
+            const int v = __shfl_sync(FULL, excl_r, own + step);
+            if (v <= ri) { own += step; own_ex = v; }
+        }
+        const uint32_t olight = __shfl_sync(FULL, light, own), oprim = __shfl_sync(FULL, prim, own);
+        int sx0 = 0, len = 0, cov0 = 1, cov1 = 0;
+        uint32_t row = 0;
+        if (ri < R) {
+            const unsigned o = wbase + (unsigned)own;
+            const GridLight* __restrict__ GL = g.lights + olight;
+            const float Gx0 = GL->x0, Gz0 = GL->z0, Gcell = GL->cell, Ginv = GL->inv_cell;
+            const int Gnx = GL->nx;
+            const float m = rec[12][o], eps = rec[13][o];
+            const int cx0 = __float_as_int(rec[14][o]), cx1 = __float_as_int(rec[15][o]), cz = __float_as_int(rec[16][o]) + (ri - own_ex);
+            const float Z0 = Gz0 + cz * Gcell - m - eps, Z1 = Gz0 + (cz + 1) * Gcell + m + eps;
+            float X0 = inf, X1 = -inf;                               // x range of the triangle within the slab
+            float i0lo = inf, i0hi = -inf, i1lo = inf, i1hi = -inf;  // x range of the triangle AT z = Z0 and AT z = Z1 (FILL)
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            float t0, t1;
-            if (dz[k] != 0.0f) { t0 = (Z0 - za[k]) * idz[k]; t1 = (Z1 - za[k]) * idz[k]; }
-            else { const bool in = za[k] >= Z0 && za[k] <= Z1; t0 = in ? -inf : inf; t1 = in ? inf : inf; }      // a horizontal edge: inside the slab or not
-            const float tlo = fmaxf(fminf(t0, t1), 0.0f), thi = fminf(fmaxf(t0, t1), 1.0f);
-            if (tlo <= thi) {                                    // the edge meets the slab (false for NaN)
-                const float xl = fmaf(tlo, dx[k], xa[k]), xh = fmaf(thi, dx[k], xa[k]);
-                X0 = fminf(X0, fminf(xl, xh)); X1 = fmaxf(X1, fmaxf(xl, xh));
+            for (int k = 0; k < 3; ++k) {
+                const float xa = rec[k][o], za = rec[3 + k][o], dx = rec[6 + k][o], idz = rec[9 + k][o];
+                float t0, t1;
+                if (idz != 0.0f) { t0 = (Z0 - za) * idz; t1 = (Z1 - za) * idz; }
+                else { const bool in = za >= Z0 && za <= Z1; t0 = in ? -inf : inf; t1 = in ? inf : inf; }      // a horizontal edge: inside the slab or not
+                const float tlo = fmaxf(fminf(t0, t1), 0.0f), thi = fminf(fmaxf(t0, t1), 1.0f);
+                if (tlo <= thi) {                                    // the edge meets the slab (false for NaN)
+                    const float xl = fmaf(tlo, dx, xa), xh = fmaf(thi, dx, xa);
+                    X0 = fminf(X0, fminf(xl, xh)); X1 = fmaxf(X1, fmaxf(xl, xh));
+                }
+                if (FILL && idz != 0.0f) {
+                    if (t0 >= 0.0f && t0 <= 1.0f) { const float xc = fmaf(t0, dx, xa); i0lo = fminf(i0lo, xc); i0hi = fmaxf(i0hi, xc); }
+                    if (t1 >= 0.0f && t1 <= 1.0f) { const float xc = fmaf(t1, dx, xa); i1lo = fminf(i1lo, xc); i1hi = fmaxf(i1hi, xc); }
+                }
             }
-            if (FILL && dz[k] != 0.0f) {
-                if (t0 >= 0.0f && t0 <= 1.0f) { const float xc = fmaf(t0, dx[k], xa[k]); i0lo = fminf(i0lo, xc); i0hi = fmaxf(i0hi, xc); }
-                if (t1 >= 0.0f && t1 <= 1.0f) { const float xc = fmaf(t1, dx[k], xa[k]); i1lo = fminf(i1lo, xc); i1hi = fmaxf(i1hi, xc); }
+            if (X0 <= X1) {                                          // the triangle reaches this row
+                sx0 = (int)floorf((X0 - m - eps - Gx0) * Ginv);
+                int sx1 = (int)floorf((X1 + m + eps - Gx0) * Ginv);
+                sx0 = max(sx0, cx0); sx1 = min(sx1, cx1);
+                len = max(sx1 - sx0 + 1, 0);
+                row = GL->cell_base + (uint32_t)cz * (uint32_t)Gnx;
+                if (FILL) {
+                    // covered cells: the dilated x range [x0 + cx cell - m, x0 + (cx + 1) cell + m] within [in_lo, in_hi], as a cell range
+                    const float in_lo = fmaxf(i0lo, i1lo) + eps, in_hi = fminf(i0hi, i1hi) - eps;
+                    if (in_lo <= in_hi) {
+                        const float nxf = (float)Gnx;
+                        cov0 = (int)fminf(fmaxf(ceilf((in_lo + m - Gx0) * Ginv), 0.0f), nxf);
+                        cov1 = (int)fminf(fmaxf(floorf((in_hi - m - Gx0) * Ginv), 0.0f), nxf) - 1;
+                    }
+                }
             }
         }
-        if (!(X0 <= X1)) continue;                               // the triangle does not reach this row
-        int sx0 = (int)floorf((X0 - m - eps - G.x0) * G.inv_cell), sx1 = (int)floorf((X1 + m + eps - G.x0) * G.inv_cell);
-        sx0 = max(sx0, cx0); sx1 = min(sx1, cx1);
-        const float in_lo = fmaxf(i0lo, i1lo) + eps, in_hi = fminf(i0hi, i1hi) - eps;      // covered cells: dilated x range within [in_lo, in_hi]
-        const uint32_t row = G.cell_base + (uint32_t)cz * (uint32_t)G.nx;
-#pragma unroll 4
-        for (int cx = sx0; cx <= sx1; ++cx) {
-            const uint32_t cell = row + (uint32_t)cx;
+        // ---- the round's spans, concatenated
+        int incl = len;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if ((int)lane >= d) incl += v; }
+        const int excl = incl - len, T = __shfl_sync(FULL, incl, 31);
+        if (!FILL) mine += (uint32_t)len;
+        constexpr int U = FILL ? 4 : 1;
+        for (int jb = 0; jb < T; jb += 32 * U) {
+            uint32_t cell[U], eprim[U], beg[U], cnt[U], old[U];
+            bool ok[U], front[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int j = jb + 32 * u + (int)lane;
+                int so = 0, so_ex = 0;                            // the last lane whose span offset is <= j (its span is not empty)
+#pragma unroll
+                for (int step = 16; step >= 1; step >>= 1) {
+                    const int v = __shfl_sync(FULL, excl, so + step);
+                    if (v <= j) { so += step; so_ex = v; }
+                }
+                const int cx = __shfl_sync(FULL, sx0, so) + (j - so_ex);
+                cell[u] = __shfl_sync(FULL, row, so) + (uint32_t)cx;
+                ok[u] = j < T;
+                if (FILL) {
+                    eprim[u] = __shfl_sync(FULL, oprim, so);
+                    const int c0 = __shfl_sync(FULL, cov0, so), c1 = __shfl_sync(FULL, cov1, so);
+                    front[u] = cx >= c0 && cx <= c1;
+                }
+            }
             if (FILL) {
                 // Order within a cell (a heuristic, any order is correct): primitives whose projection covers the whole
                 // cell go to the front, the others to the back -- a ray that reads the cell is then more often occluded by
                 // the first primitive it tests.  One counter, front count in the low and back count in the
                 // high half (cells with >= 2^16 entries are filled front to back only).
-                const float rx0 = G.x0 + cx * G.cell - m, rx1 = G.x0 + (cx + 1) * G.cell + m;
-                const bool covers = rx0 >= in_lo && rx1 <= in_hi;
-                const uint32_t beg = g.cell_start[cell], cnt = g.cell_start[cell + 1] - beg;
-                uint32_t pos;
-                if (cnt >= 65536u || covers) pos = beg + (atomicAdd(g.cell_fill + cell, 1u) & (cnt >= 65536u ? 0xffffffffu : 0xffffu));
-                else pos = beg + cnt - 1u - (atomicAdd(g.cell_fill + cell, 0x10000u) >> 16);
-                if ((uint64_t)pos < g.entries_alloc) g.entries[pos] = (int)prim;
-            } else {
-                atomicAdd(g.cell_fill + cell, 1u);
-                ++mine;
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    beg[u] = 0u; cnt[u] = 0u;
+                    if (ok[u]) { beg[u] = g.cell_start[cell[u]]; cnt[u] = g.cell_start[cell[u] + 1] - beg[u]; }
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    old[u] = 0u;
+                    front[u] = front[u] || cnt[u] >= 65536u;
+                    if (ok[u]) old[u] = atomicAdd(g.cell_fill + cell[u], front[u] ? 1u : 0x10000u);
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (ok[u]) {
+                        const uint32_t pos = front[u] ? beg[u] + (old[u] & (cnt[u] >= 65536u ? 0xffffffffu : 0xffffu)) : beg[u] + cnt[u] - 1u - (old[u] >> 16);
+                        if ((uint64_t)pos < g.entries_alloc) g.entries[pos] = (int)eprim[u];
+                    }
+                }
+            } else if (ok[0]) {
+                atomicAdd(g.cell_fill + cell[0], 1u);
             }
         }
     }
-    }
     if (!FILL) {                                                  // 64-bit total of the counts, one atomic per warp
-        const uint32_t tot = __reduce_add_sync(0xffffffffu, mine);
-        if ((threadIdx.x & 31) == 0 && tot) atomicAdd(reinterpret_cast<unsigned long long*>(g.ctl + 6), (unsigned long long)tot);
+        const uint32_t tot = __reduce_add_sync(FULL, mine);
+        if (lane == 0 && tot) atomicAdd(reinterpret_cast<unsigned long long*>(g.ctl + 6), (unsigned long long)tot);
     }
 }
 
@@ -778,7 +861,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     g.cell_cap = (uint32_t)CELL_CAP;
     const unsigned nmax = n_lights > n_tris ? (n_lights > 12 ? n_lights : 12) : (n_tris > 12 ? n_tris : 12);
     const unsigned gw = (unsigned)((work + 255) / 256);
-    const unsigned gr = (unsigned)((work * RTB_RASTER_SPLIT + 255) / 256);     // k_grid_raster: RTB_RASTER_SPLIT threads per pair
+    const unsigned gr = gw;                                                    // k_grid_raster: one thread per pair
     G.builds++;
 
     // ---- speculative form -------------------------------------------------------------------------------------------------
