@@ -174,7 +174,8 @@ class SharedHostFrame:
                 shared_memory.SharedMemory(name=self.name).unlink()
             except Exception:
                 pass
-            self.shm = shared_memory.SharedMemory(name=self.name, create=True, size=nbytes)
+            self.shm = shared_memory.SharedMemory(name=self.name, create=True, size=nbytes + 64 * world)
+            np.ndarray((8 * world,), dtype=np.int64, buffer=self.shm.buf, offset=nbytes)[:] = 0
         if world > 1:
             import torch.distributed as dist
             dist.barrier()
@@ -184,13 +185,29 @@ class SharedHostFrame:
         self.array[:1] = self.array[:1]
         self.ptr = self.array.ctypes.data
         self.nbytes = nbytes
+        # "my rows of step k have landed": one cache line per rank behind the frame, read by everybody (host_barrier)
+        self.world = world
+        self.landed = np.ndarray((world, 8), dtype=np.int64, buffer=self.shm.buf, offset=nbytes)
         rc = torch.cuda.cudart().cudaHostRegister(self.ptr, nbytes, 0)
         self.registered = int(rc) == 0
         if not self.registered:
             raise SystemExit("cudaHostRegister failed: %r" % (rc,))
 
+    def host_barrier(self, step, timeout_s=60.0):
+        """Returns when every rank has finished step `step` (its rows are in the shared frame: rtb_render_end has returned).  A
+        host-side rendezvous through the shared allocation itself: the step ends with the complete frame in host memory, and
+        nothing about that needs the GPUs (an NCCL barrier costs a kernel launch and a stream synchronisation per step)."""
+        self.landed[self.rank, 0] = step
+        if self.world == 1:
+            return
+        t0 = time.perf_counter()
+        while int(self.landed[:, 0].min()) < step:
+            if time.perf_counter() - t0 > timeout_s:
+                raise SystemExit("host_barrier: a rank did not finish step %d" % step)
+
     def close(self):
         import torch
+        self.landed = None
         if self.registered:
             torch.cuda.cudart().cudaHostUnregister(self.ptr)
             self.registered = False
@@ -387,21 +404,29 @@ def main():
         tag = os.environ.get("MASTER_PORT", "0") + "_" + str(os.getppid() if world > 1 else os.getpid())
         shared = SharedHostFrame(H * W * 3, rank, world, tag)
         out_np = shared.array.reshape(H, W, 3)
-        h_smp = torch.from_numpy(samples).pin_memory()
-        smp_np = h_smp.numpy()
+        # two pinned copies of the table, used in turn: the copy a frame in flight reads is not the one handed over for the next
+        h_smp = [torch.from_numpy(samples).pin_memory() for _ in range(2)]
+        smp_np = [h.numpy() for h in h_smp]
+        rkw = dict(width=W, height=H, band_rows=BAND_ROWS, rank=rank, world=world, frame_rows=(world > 1), **kw)
+        n_e2e = [0]
 
         def e2e_step():
-            scene.set_samples_async(smp_np)
-            return scene.render(out=out_np, width=W, height=H, band_rows=BAND_ROWS, rank=rank, world=world, frame_rows=(world > 1), **kw)[1]
+            # the step's table was handed over during the previous step (or just before the loop): its H2D copy, light tables and
+            # light grids ran next to that step's kernels; this step does the same for the next one
+            k = n_e2e[0]; n_e2e[0] += 1
+            scene.render_begin(out_np, **rkw)
+            scene.set_samples_async(smp_np[(k + 1) & 1])
+            se = scene.render_end()[1]
+            shared.host_barrier(k + 1)               # "every rank's rows have landed": the step ends with the full frame on the host
+            return se
 
+        scene.set_samples_async(smp_np[0])
         for _ in range(2):
             e2e_step()
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             se = e2e_step()
-            if world > 1:
-                dist.barrier()                       # "every rank's rows have landed": the step ends with the full frame on the host
         barrier()
         e2e_s = allmax(time.perf_counter() - t0)
         if rank == 0:
@@ -417,8 +442,9 @@ def main():
         barrier()
         shared.close()
         h2d, d2h = world * int(samples.nbytes + 64), H * W * 3
-        e2e_path = ("rtb_scene_set_samples_async + rtb_render (RTB_FLAG_FRAME_ROWS) per rank: pinned sample table in, every rank's rows "
-                    "copied device-to-host into one shared pinned host frame; light grids rebuilt every step (new table)")
+        e2e_path = ("per rank and step: rtb_render_begin (RTB_FLAG_FRAME_ROWS) / rtb_scene_set_samples_async (the NEXT step's pinned table: "
+                    "H2D + light-grid rebuild next to this step's kernels) / rtb_render_end; every rank's rows copied device-to-host into one "
+                    "shared pinned host frame, host-side rendezvous per step; light grids rebuilt every step (new table)")
         launches_per_step = s1["launches"] * world + (1 if (world > 1 and not use_peer) else 0)
         parallelism = ("row bands b %% N over %d GPU(s), scene replicated, " % world) + (
             "k_shade stores into rank 0's frame over NVLink peer memory (one kernel renders and gathers)" if use_peer

@@ -158,6 +158,20 @@ int rtb_scene_set_samples_async(rtb_scene* scene, const float* samples, uint32_t
  *     Blocking.  stats may be NULL. */
 int rtb_render(rtb_scene* scene, const rtb_render_params* params, uint8_t* rgb8, rtb_stats* stats);
 
+/* rtb_render in two halves, for a caller that renders frame after frame, each with its own sample table (the reference draws a
+ * fresh table in every render(), src/main.rs:260-265, and its orbit loop calls render() per frame, src/main.rs:319-362).
+ *   rtb_render_begin  enqueues the frame and returns; rgb8 must be PINNED host memory and stay valid until rtb_render_end.
+ *   rtb_scene_set_samples_async called between the two (pinned table) is the table of the NEXT frame: it goes into the scene's
+ *                     spare table set, and its upload, light tables and light grids run next to the kernels of the frame in
+ *                     flight (same parameters assumed; others are rebuilt by the next begin).  The table must stay valid until
+ *                     the rtb_render_end of the frame that uses it.
+ *   rtb_render_end    waits for the frame: rgb8 is complete when it returns.  Should a speculative grid rebuild not have fitted,
+ *                     it is redone here and the frame rendered once more before returning (stats->grid_redo = 1).
+ * One frame in flight per scene; every other render / set_samples call on the scene fails with RTB_ERR_STATE until rtb_render_end.
+ * Frames are bit-identical to rtb_render with the same table. */
+int rtb_render_begin(rtb_scene* scene, const rtb_render_params* params, uint8_t* rgb8);
+int rtb_render_end(rtb_scene* scene, rtb_stats* stats);
+
 /* render() on several GPUs of one box from ONE host thread's point of view (the reference's render fans out to its worker threads
  * and joins them itself, src/main.rs:269-303): scenes[i] is the same scene created on device i (rtb_scene_desc.device), all with the
  * same sample table (rtb_scene_set_samples[_async] on each, or rtb_scenes_set_samples).  Band b of params->band_rows rows (0 = 4)

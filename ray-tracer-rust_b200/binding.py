@@ -78,7 +78,7 @@ class SequenceStats(C.Structure):
 
 
 EXPORTS = ["rtb_import_obj_parallel", "rtb_free_pinned", "rtb_color_to_u8_static", "rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
-           "rtb_render_sequence", "rtb_render_sequence_multi", "rtb_measure_peaks", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render",
+           "rtb_render_sequence", "rtb_render_sequence_multi", "rtb_measure_peaks", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render", "rtb_render_begin", "rtb_render_end",
            "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj", "rtb_import_obj_ex",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
 
@@ -107,6 +107,8 @@ def lib():
         L.rtb_scene_set_samples.argtypes = [vp, vp, C.c_uint32]
         L.rtb_scene_set_materials.argtypes = [vp, vp]
         L.rtb_render.argtypes = [vp, vp, vp, vp]
+        L.rtb_render_begin.argtypes = [vp, vp, vp]
+        L.rtb_render_end.argtypes = [vp, vp]
         L.rtb_render_device.argtypes = [vp, vp, vp, vp]
         L.rtb_render_pixels.argtypes = [vp, vp, vp, C.c_uint64, vp, vp, vp, vp, vp, vp]
         L.rtb_color_to_u8.argtypes = [vp, vp, C.c_uint64, vp]
@@ -307,6 +309,7 @@ class Scene:
         """rtb_scene_set_samples_async: `samples` must be pinned host memory that stays valid until the next render returns."""
         s = np.ascontiguousarray(samples, np.float32).reshape(-1, 2)
         _check(lib().rtb_scene_set_samples_async(self._h, _ptr(s), s.shape[0]))
+        self._samples_prev = getattr(self, "_samples", None)      # a frame in flight may still be reading the previous table
         self._samples = s
 
     def render_sequence(self, poses, frames=None, png_pattern=None, **kw):
@@ -355,6 +358,21 @@ class Scene:
             out = np.empty((rows, p.width, 3), np.uint8)
         st = Stats()
         _check(lib().rtb_render(self._h, C.byref(p), _ptr(out), C.byref(st)))
+        return out, st.as_dict()
+
+    def render_begin(self, out, **kw):
+        """First half of render(): enqueues the frame into the PINNED array `out` and returns (rtb_render_begin).  A
+        set_samples_async() before render_end() hands over the next frame's table."""
+        p = self.params(**kw)
+        self._inflight = (p, out)                       # both must outlive the frame
+        _check(lib().rtb_render_begin(self._h, C.byref(p), _ptr(out)))
+
+    def render_end(self):
+        """Second half: waits for the frame begun with render_begin -> (out, stats)."""
+        st = Stats()
+        _check(lib().rtb_render_end(self._h, C.byref(st)))
+        p, out = self._inflight
+        self._inflight = None
         return out, st.as_dict()
 
     def color_to_u8(self, linear):

@@ -14,6 +14,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <utility>
 #include <vector>
 #include <chrono>
 
@@ -26,6 +27,7 @@ cudaError_t rtb_grid_scene_stats(RtbGrid&, const float4*, uint32_t, cudaStream_t
 cudaError_t rtb_grid_build(RtbGrid&, const float4*, uint32_t, const float4*, uint32_t, float, bool, cudaStream_t);
 cudaError_t rtb_cam_grid_build(RtbGrid&, const float4*, uint32_t, float4*, float4*, const CameraBasis&, float, bool, cudaStream_t);
 cudaError_t rtb_grid_validate(RtbGrid&, cudaStream_t, bool*);
+cudaError_t rtb_grid_sort_on_reuse(RtbGrid&, cudaStream_t);
 void rtb_grid_free(RtbGrid&);
 cudaError_t rtb_launch_light_table(const float2*, uint32_t, const float*, float4*, float*, cudaStream_t);
 cudaError_t rtb_launch_light_groups(const float4*, const float*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint16_t*, float*, cudaStream_t);
@@ -104,7 +106,36 @@ struct rtb_scene {
     uint8_t* d_full; size_t full_cap;
     // rtb_render_sequence: two device frames, two pinned host frames, snapshots of the camera grid's control words
     uint8_t* d_seq[2]; uint8_t* h_seq[2]; size_t seq_cap; uint32_t* h_seq_ctl; cudaEvent_t ev_seq[2], ev_seq0, ev_seq1;
+    // Everything that is derived from ONE sample table: the table, its light tables and its light grids.  The scene owns two such
+    // sets -- the members above are the current one, `alt` the spare -- so that the table of the NEXT frame can be uploaded and its
+    // grids built (on build_stream) while the kernels of a frame begun with rtb_render_begin still read the current set.
+    struct TableSet {
+        float2* d_samples; uint32_t n_samples; float4* d_light_pts; uint32_t light_pts_cap; uint16_t* d_light_perm; size_t light_perm_cap;
+        float* d_light_gbox; size_t light_gbox_cap; float* d_light_box; RtbGrid grid; uint64_t samples_version;
+        bool light_key_set; uint64_t light_key_samples, light_key_need; uint32_t light_key_nb_ray, light_key_nls; cudaStream_t light_key_stream;
+        cudaEvent_t ev_prefix, ev_samples; bool samples_pending; uint32_t samples_prefix;
+    } alt;
+    bool alt_inited, alt_ready;                  // alt_ready: alt holds a prefetched table, the next rtb_render_begin takes it
+    cudaStream_t build_stream; cudaEvent_t ev_built;
+    uint64_t version_counter;                    // source of samples_version (unique across both sets)
+    uint32_t prefetch_rebuilds;
+    // rtb_render_begin .. rtb_render_end
+    struct Pending {
+        bool active; rtb_render_params p; uint8_t* h_rgb8; uint8_t* d_full; TraceArgs a; uint8_t* stage; bool h_frame_rows; uint32_t rebuilds;
+    } pend;
 };
+
+static void swap_table_sets(rtb_scene* s) {
+    rtb_scene::TableSet& t = s->alt;
+    std::swap(s->d_samples, t.d_samples); std::swap(s->n_samples, t.n_samples); std::swap(s->d_light_pts, t.d_light_pts);
+    std::swap(s->light_pts_cap, t.light_pts_cap); std::swap(s->d_light_perm, t.d_light_perm); std::swap(s->light_perm_cap, t.light_perm_cap);
+    std::swap(s->d_light_gbox, t.d_light_gbox); std::swap(s->light_gbox_cap, t.light_gbox_cap); std::swap(s->d_light_box, t.d_light_box);
+    std::swap(s->grid, t.grid); std::swap(s->samples_version, t.samples_version);
+    std::swap(s->light_key_set, t.light_key_set); std::swap(s->light_key_samples, t.light_key_samples); std::swap(s->light_key_need, t.light_key_need);
+    std::swap(s->light_key_nb_ray, t.light_key_nb_ray); std::swap(s->light_key_nls, t.light_key_nls); std::swap(s->light_key_stream, t.light_key_stream);
+    std::swap(s->ev_prefix, t.ev_prefix); std::swap(s->ev_samples, t.ev_samples); std::swap(s->samples_pending, t.samples_pending);
+    std::swap(s->samples_prefix, t.samples_prefix);
+}
 
 // ---- Color::to_rgba threshold table (color.rs:10-33) ---------------------------------------
 static uint8_t host_gamma_u8(float linear) {
@@ -181,6 +212,12 @@ void rtb_scene_destroy(rtb_scene* s) {
     if (s->h_seq_ctl) cudaFreeHost(s->h_seq_ctl);
     if (s->ev_seq0) cudaEventDestroy(s->ev_seq0);
     if (s->ev_seq1) cudaEventDestroy(s->ev_seq1);
+    cudaFree(s->alt.d_samples); cudaFree(s->alt.d_light_pts); cudaFree(s->alt.d_light_perm); cudaFree(s->alt.d_light_gbox); cudaFree(s->alt.d_light_box);
+    rtb_grid_free(s->alt.grid);
+    if (s->alt.ev_prefix) cudaEventDestroy(s->alt.ev_prefix);
+    if (s->alt.ev_samples) cudaEventDestroy(s->alt.ev_samples);
+    if (s->build_stream) cudaStreamDestroy(s->build_stream);
+    if (s->ev_built) cudaEventDestroy(s->ev_built);
     if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
     if (s->ev_prefix) cudaEventDestroy(s->ev_prefix);
     if (s->ev_samples) cudaEventDestroy(s->ev_samples);
@@ -314,7 +351,9 @@ int rtb_scene_get_info(const rtb_scene* s, rtb_scene_info* info) {
 
 int rtb_scene_set_samples(rtb_scene* s, const float* samples, uint32_t n_pairs) {
     if (!s || !samples || n_pairs == 0) return fail(RTB_ERR_ARG, "rtb_scene_set_samples: null/empty table");
+    if (s->pend.active) return fail(RTB_ERR_STATE, "rtb_scene_set_samples: a frame is in flight (rtb_render_begin); use rtb_scene_set_samples_async with a pinned table");
     CUDA_TRY(cudaSetDevice(s->device));
+    s->alt_ready = false;                         // a table prefetched earlier is superseded
     if (n_pairs != s->n_samples) {
         cudaFree(s->d_samples); s->d_samples = nullptr; s->n_samples = 0;
         CUDA_TRY(cudaMalloc(&s->d_samples, (size_t)n_pairs * sizeof(float2)));
@@ -323,9 +362,11 @@ int rtb_scene_set_samples(rtb_scene* s, const float* samples, uint32_t n_pairs) 
     s->samples_pending = false;
     CUDA_TRY(cudaMemcpyAsync(s->d_samples, samples, (size_t)n_pairs * sizeof(float2), cudaMemcpyHostToDevice, s->stream));
     CUDA_TRY(cudaStreamSynchronize(s->stream));
-    s->samples_version++;
+    s->samples_version = ++s->version_counter;
     return RTB_OK;
 }
+
+static int prefetch_samples(rtb_scene* s, const float* samples, uint32_t n_pairs);
 
 #define RTB_SAMPLES_PREFIX 65536u      // pairs uploaded first (512 KB): far more than any frame's light points (nb_ray^2 + nb_light_sample)
 
@@ -335,6 +376,8 @@ int rtb_scene_set_samples_async(rtb_scene* s, const float* samples, uint32_t n_p
     const bool pinned = cudaPointerGetAttributes(&pa, samples) == cudaSuccess && pa.type == cudaMemoryTypeHost;
     if (!pinned) { cudaGetLastError(); return rtb_scene_set_samples(s, samples, n_pairs); }
     CUDA_TRY(cudaSetDevice(s->device));
+    if (s->pend.active) return prefetch_samples(s, samples, n_pairs);       // a frame is in flight: the table of the NEXT frame
+    s->alt_ready = false;                         // a table prefetched earlier is superseded
     if (n_pairs != s->n_samples) {
         CUDA_TRY(cudaStreamSynchronize(s->stream));
         cudaFree(s->d_samples); s->d_samples = nullptr; s->n_samples = 0;
@@ -352,20 +395,16 @@ int rtb_scene_set_samples_async(rtb_scene* s, const float* samples, uint32_t n_p
                                  cudaMemcpyHostToDevice, s->copy_stream));
     CUDA_TRY(cudaEventRecord(s->ev_samples, s->copy_stream));
     s->samples_pending = true; s->samples_prefix = prefix;
-    s->samples_version++;
+    s->samples_version = ++s->version_counter;
     return RTB_OK;
 }
 
 }  // extern "C"
 
-// Validates params, (re)builds the light-point table on `st`, fills TraceArgs.
-static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t st, TraceArgs* a, bool allow_spec = false) {
-    if (!s || !p) return fail(RTB_ERR_ARG, "render: null argument");
-    if (!s->d_samples) return fail(RTB_ERR_STATE, "render: rtb_scene_set_samples has not been called");
-    if (p->width == 0 || p->height == 0) return fail(RTB_ERR_ARG, "render: empty frame");
-    const uint32_t world = p->world ? p->world : 1;
-    if (world > 1 && (p->band_rows == 0 || p->rank >= world)) return fail(RTB_ERR_ARG, "render: bad band ownership");
-    CUDA_TRY(cudaSetDevice(s->device));
+// What a frame derives from the current sample table, (re)built on `st` where it is not cached: the light-point tables (points,
+// pairs, bounds, sorted groups) and the light grids.
+struct TableInfo { uint64_t need; uint32_t n_groups, group_size; bool use_perm; };
+static int build_tables(rtb_scene* s, const rtb_render_params* p, cudaStream_t st, bool allow_spec, TableInfo* ti) {
     // light points used by a frame: indices (r*nb_ray + i) % n_samples, r < nb_ray, i < nb_light_sample
     uint64_t need = p->nb_ray ? (uint64_t)(p->nb_ray - 1) * p->nb_ray + p->nb_light_sample : 0;
     if (need > s->n_samples) need = s->n_samples;
@@ -379,9 +418,8 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     const bool lights_cached = s->light_key_set && s->light_key_samples == s->samples_version && s->light_key_need == need &&
                                s->light_key_nb_ray == p->nb_ray && s->light_key_nls == p->nb_light_sample && s->light_key_stream == st;
     s->light_tables_ran = !lights_cached;
-    s->grid_rebuilds = 0;
     if (s->samples_pending) {                     // asynchronous table upload: the light tables need its prefix only
-        if (st != s->stream) CUDA_TRY(cudaStreamWaitEvent(st, s->ev_prefix, 0));
+        CUDA_TRY(cudaStreamWaitEvent(st, s->ev_prefix, 0));
         if (need > s->samples_prefix) CUDA_TRY(cudaStreamWaitEvent(st, s->ev_samples, 0));
     }
     if (!lights_cached) CUDA_TRY(rtb_launch_light_table(s->d_samples, (uint32_t)need, s->light, s->d_light_pts, s->d_light_box, st));
@@ -416,10 +454,91 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     // light grids: one per light point the frame addresses; cached until the table or that count changes
     if (s->shadow_mode != 1 && p->nb_ray && p->nb_light_sample &&
         !(s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need)) {
+        const uint32_t w = p->world ? p->world : 1;
+        const uint64_t share_rays = (uint64_t)rtb_owned_rows(p->height, w > 1 ? p->band_rows : p->height, w > 1 ? p->rank : 0, w) * p->width * p->nb_ray;
+        s->grid.sort_at_build = share_rays >= (48ull << 20);        // the ordering pass repays itself within this frame (rtb_grid.cu, pass E)
         CUDA_TRY(rtb_grid_build(s->grid, s->d_tris, s->n_tris, s->d_light_pts, (uint32_t)need, s->grid_cell_factor, allow_spec, st));
         s->grid_rebuilds++;
         s->grid.key_set = true; s->grid.key_samples = s->samples_version; s->grid.key_n_lights = (uint32_t)need;
+    } else if (s->shadow_mode != 1 && p->nb_ray && p->nb_light_sample) {
+        CUDA_TRY(rtb_grid_sort_on_reuse(s->grid, st));             // the second frame of a table: the lists get their full order
     }
+    ti->need = need; ti->n_groups = n_groups; ti->group_size = group_size; ti->use_perm = use_perm;
+    return RTB_OK;
+}
+
+// rtb_scene_set_samples_async while a frame begun with rtb_render_begin is in flight: the table goes into the spare set, and the
+// light tables and light grids of the in-flight frame's parameters are built from it on build_stream, next to that frame's
+// kernels (which read the current set only).  The next rtb_render_begin swaps the sets and waits for ev_built.
+static int prefetch_samples(rtb_scene* s, const float* samples, uint32_t n_pairs) {
+    if (!s->alt_inited) {
+        rtb_scene::TableSet& t = s->alt;
+        CUDA_TRY(cudaStreamCreateWithFlags(&s->build_stream, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&s->ev_built, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&t.ev_prefix, cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&t.ev_samples, cudaEventDisableTiming));
+        CUDA_TRY(cudaMalloc(&t.d_light_box, 8 * sizeof(float)));
+        t.grid.entry_cap_limit = s->grid.entry_cap_limit;
+        t.grid.y_min = s->grid.y_min; t.grid.mean_extent = s->grid.mean_extent; t.grid.stats_ok = s->grid.stats_ok;
+        s->alt_inited = true;
+    }
+    s->alt_ready = false;
+    swap_table_sets(s);                           // the members below are the SPARE set now (the frame in flight took its pointers by value)
+    int rc = RTB_OK;
+    cudaError_t e = cudaSuccess;
+    do {
+        if (n_pairs != s->n_samples) {
+            cudaFree(s->d_samples); s->d_samples = nullptr; s->n_samples = 0;
+            if ((e = cudaMalloc(&s->d_samples, (size_t)n_pairs * sizeof(float2))) != cudaSuccess) break;
+            s->n_samples = n_pairs;
+        }
+        // whatever was enqueued for this set before (an earlier prefetch nobody rendered) is ahead of us on build_stream; the tail
+        // copy on copy_stream starts behind it too
+        if ((e = cudaEventRecord(s->ev_idle, s->build_stream)) != cudaSuccess) break;
+        if ((e = cudaStreamWaitEvent(s->copy_stream, s->ev_idle, 0)) != cudaSuccess) break;
+        const uint32_t prefix = n_pairs < RTB_SAMPLES_PREFIX ? n_pairs : RTB_SAMPLES_PREFIX;
+        if ((e = cudaMemcpyAsync(s->d_samples, samples, (size_t)prefix * sizeof(float2), cudaMemcpyHostToDevice, s->build_stream)) != cudaSuccess) break;
+        if ((e = cudaEventRecord(s->ev_prefix, s->build_stream)) != cudaSuccess) break;
+        if (n_pairs > prefix &&
+            (e = cudaMemcpyAsync(s->d_samples + prefix, samples + 2 * (size_t)prefix, (size_t)(n_pairs - prefix) * sizeof(float2),
+                                 cudaMemcpyHostToDevice, s->copy_stream)) != cudaSuccess) break;
+        if ((e = cudaEventRecord(s->ev_samples, s->copy_stream)) != cudaSuccess) break;
+        s->samples_pending = true; s->samples_prefix = prefix;
+        s->samples_version = ++s->version_counter;
+        const uint32_t before = s->grid_rebuilds;
+        s->grid_rebuilds = 0;
+        TableInfo ti;
+        rc = build_tables(s, &s->pend.p, s->build_stream, !getenv("RTB200_NO_SPEC"), &ti);
+        s->prefetch_rebuilds = s->grid_rebuilds; s->grid_rebuilds = before;
+        if (rc != RTB_OK) break;
+        s->light_key_stream = s->stream;          // the frame that uses the set waits for ev_built on its own stream: same ordering
+        e = cudaEventRecord(s->ev_built, s->build_stream);
+    } while (0);
+    swap_table_sets(s);                           // back: the current set is the in-flight frame's again
+    if (rc != RTB_OK) return rc;
+    if (e != cudaSuccess) return fail(RTB_ERR_CUDA, "rtb_scene_set_samples_async (prefetch): %s", cudaGetErrorString(e));
+    s->alt_ready = true;
+    return RTB_OK;
+}
+
+// Validates params, (re)builds the light-point table on `st`, fills TraceArgs.
+static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t st, TraceArgs* a, bool allow_spec = false) {
+    if (!s || !p) return fail(RTB_ERR_ARG, "render: null argument");
+    if (!s->d_samples) return fail(RTB_ERR_STATE, "render: rtb_scene_set_samples has not been called");
+    if (s->pend.active) return fail(RTB_ERR_STATE, "render: a frame begun with rtb_render_begin is in flight (rtb_render_end first)");
+    if (p->width == 0 || p->height == 0) return fail(RTB_ERR_ARG, "render: empty frame");
+    const uint32_t world = p->world ? p->world : 1;
+    if (world > 1 && (p->band_rows == 0 || p->rank >= world)) return fail(RTB_ERR_ARG, "render: bad band ownership");
+    CUDA_TRY(cudaSetDevice(s->device));
+    s->grid_rebuilds = 0;
+    TableInfo ti;
+    {
+        const int rc = build_tables(s, p, st, allow_spec, &ti);
+        if (rc != RTB_OK) return rc;
+    }
+    const uint64_t need = ti.need;
+    const uint32_t n_groups = ti.n_groups, group_size = ti.group_size;
+    const bool use_perm = ti.use_perm;
     CUDA_TRY(cudaMemsetAsync(s->d_counters, 0, RTB_NUM_CTRS * sizeof(unsigned long long), st));
     memset(a, 0, sizeof(*a));
     a->tris = s->d_tris; a->colors = s->d_colors4; a->ksns = s->d_ksns; a->nodes = s->d_nodes; a->samples = s->d_samples; a->light_pts = s->d_light_pts; a->light_pairs = s->d_light_pts + need; a->light_box = s->d_light_box;
@@ -427,7 +546,7 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     a->light_gbox = s->d_light_gbox; a->n_groups = n_groups; a->group_size = group_size;
     if (s->shadow_mode != 1 && s->grid.valid && s->grid.key_set && s->grid.key_samples == s->samples_version && s->grid.key_n_lights == (uint32_t)need) {
         a->grid_lights = s->grid.d_lights; a->grid_cell_start = s->grid.d_cell_start; a->grid_entries = s->grid.d_entries;
-        a->grid_big = s->grid.d_big; a->grid_n_big = s->grid.n_big;
+        a->grid_big = s->grid.d_big; a->grid_n_big = s->grid.n_big; a->grid_entry_mask = s->grid.keyed ? 0xffffff : -1;
         a->grid_union = s->grid.d_union; a->grid_sat = s->grid.d_sat;
     }
     a->n_tris = s->n_tris; a->n_samples = s->n_samples; a->n_light_pts = (uint32_t)need; a->root = s->root;
@@ -443,10 +562,12 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
             CUDA_TRY(rtb_cam_grid_build(s->cam_grid, s->d_tris, s->n_tris, s->d_cam_tris, s->d_cam_origin, a->cam, s->cam_cell_px, allow_spec, st));
             s->grid_rebuilds++;
             s->cam_key = a->cam; s->cam_key_set = true;
+        } else {
+            CUDA_TRY(rtb_grid_sort_on_reuse(s->cam_grid, st));
         }
         if (s->cam_grid.valid) {
             a->cam_grid = s->cam_grid.d_lights; a->cam_cell_start = s->cam_grid.d_cell_start; a->cam_entries = s->cam_grid.d_entries;
-            a->cam_big = s->cam_grid.d_big; a->cam_n_big = s->cam_grid.n_big;
+            a->cam_big = s->cam_grid.d_big; a->cam_n_big = s->cam_grid.n_big; a->cam_entry_mask = s->cam_grid.keyed ? 0xffffff : -1;
         }
     }
     a->denom = (float)(p->nb_ray * p->nb_light_sample);
@@ -730,70 +851,139 @@ int rtb_peer_close(int32_t device, void* d_ptr, int32_t owner) {
 // The light grids / camera grid a new table / camera needs are rebuilt speculatively (rtb_grid.cu: no host synchronisation
 // between the build's passes and the frame's kernels); after the frame's one synchronisation the builds are validated and, should
 // one not have fitted its allocation, rebuilt synchronously and the frame rendered once more.
-static int render_core(rtb_scene* s, const rtb_render_params* p, uint8_t* h_rgb8, uint8_t* d_full, rtb_stats* stats) {
-    if (!s || !p) return fail(RTB_ERR_ARG, "render: null argument");
-    s->grid_redo = 0;
-    uint32_t rebuilds = 0;
-    for (int attempt = 0; ; ++attempt) {
-        TraceArgs a;
-        int rc = prepare_args(s, p, s->stream, &a, attempt == 0 && !getenv("RTB200_NO_SPEC"));
-        if (rc != RTB_OK) return rc;
-        rebuilds += s->grid_rebuilds;
-        const size_t bytes = (size_t)a.owned_rows * a.width * 3;
-        const bool h_frame_rows = !d_full && (p->flags & RTB_FLAG_FRAME_ROWS) != 0 && a.world > 1;
-        if (!d_full && bytes > s->frame_cap) {
-            cudaFree(s->d_frame); s->d_frame = nullptr; s->frame_cap = 0;
-            CUDA_TRY(cudaMalloc(&s->d_frame, bytes));
-            s->frame_cap = bytes;
-        }
-        a.rgb8 = d_full ? d_full : s->d_frame;
-        a.frame_rows = d_full ? 1u : 0u;
-        CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
-        // a pinned destination takes per-chunk copies (an asynchronous copy to pageable memory would block the host chunk by chunk)
-        bool pinned = false;
-        if (h_rgb8) {
-            cudaPointerAttributes pa;
-            pinned = cudaPointerGetAttributes(&pa, h_rgb8) == cudaSuccess && pa.type == cudaMemoryTypeHost && !(p->flags & RTB_FLAG_PROFILE);
-            if (!pinned) cudaGetLastError();
-        }
-        rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0, pinned ? h_rgb8 : nullptr, h_frame_rows);
-        if (rc != RTB_OK) return rc;
-        if (s->grid.fill_async) CUDA_TRY(cudaStreamWaitEvent(s->stream, s->grid.ev_fill, 0));    // (frames without shadow kernels never waited for it)
-        CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
-        uint8_t* stage = nullptr;
-        if (h_rgb8 && bytes && !pinned) {
-            if (h_frame_rows) {                    // pageable full frame: compact rows through the scene's pinned buffer, placed by the host below
-                if (bytes > s->pinned_cap) {
-                    if (s->h_pinned) cudaFreeHost(s->h_pinned);
-                    s->h_pinned = nullptr; s->pinned_cap = 0;
-                    CUDA_TRY(cudaMallocHost(&s->h_pinned, bytes));
-                    s->pinned_cap = bytes;
-                }
-                stage = s->h_pinned;
-                CUDA_TRY(cudaMemcpyAsync(stage, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
-            } else {
-                CUDA_TRY(cudaMemcpyAsync(h_rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
+// render_enqueue: everything of one attempt up to (not including) the host's wait; render_finish: the wait, the verdict of the
+// speculative builds (*redo) and, for a pageable full-frame destination, the placement of the staged rows.
+static int render_enqueue(rtb_scene* s, const rtb_render_params* p, uint8_t* h_rgb8, uint8_t* d_full, bool first, rtb_scene::Pending* pr) {
+    const bool allow_spec = first && !getenv("RTB200_NO_SPEC");
+    pr->p = *p; pr->h_rgb8 = h_rgb8; pr->d_full = d_full; pr->stage = nullptr; pr->rebuilds = 0;
+    // a table prefetched during the previous frame: its set becomes the current one (a redo renders the SAME table again: the
+    // prefetched one waits for the next frame)
+    if (first && s->alt_ready) {
+        CUDA_TRY(cudaSetDevice(s->device));
+        swap_table_sets(s);
+        s->alt_ready = false;
+        CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_built, 0));
+        pr->rebuilds += s->prefetch_rebuilds; s->prefetch_rebuilds = 0;
+    }
+    TraceArgs& a = pr->a;
+    int rc = prepare_args(s, p, s->stream, &a, allow_spec);
+    if (rc != RTB_OK) return rc;
+    pr->rebuilds += s->grid_rebuilds;
+    const size_t bytes = (size_t)a.owned_rows * a.width * 3;
+    const bool h_frame_rows = !d_full && (p->flags & RTB_FLAG_FRAME_ROWS) != 0 && a.world > 1;
+    pr->h_frame_rows = h_frame_rows;
+    if (!d_full && bytes > s->frame_cap) {
+        cudaFree(s->d_frame); s->d_frame = nullptr; s->frame_cap = 0;
+        CUDA_TRY(cudaMalloc(&s->d_frame, bytes));
+        s->frame_cap = bytes;
+    }
+    a.rgb8 = d_full ? d_full : s->d_frame;
+    a.frame_rows = d_full ? 1u : 0u;
+    CUDA_TRY(cudaEventRecord(s->ev0, s->stream));
+    // a pinned destination takes per-chunk copies (an asynchronous copy to pageable memory would block the host chunk by chunk)
+    bool pinned = false;
+    if (h_rgb8) {
+        cudaPointerAttributes pa;
+        pinned = cudaPointerGetAttributes(&pa, h_rgb8) == cudaSuccess && pa.type == cudaMemoryTypeHost && !(p->flags & RTB_FLAG_PROFILE);
+        if (!pinned) cudaGetLastError();
+    }
+    rc = run_wavefront(s, a, (p->flags & RTB_FLAG_COUNTERS) != 0, s->stream, (p->flags & RTB_FLAG_PROFILE) != 0, pinned ? h_rgb8 : nullptr, h_frame_rows);
+    if (rc != RTB_OK) return rc;
+    if (s->grid.fill_async) CUDA_TRY(cudaStreamWaitEvent(s->stream, s->grid.ev_fill, 0));    // (frames without shadow kernels never waited for it)
+    CUDA_TRY(cudaEventRecord(s->ev1, s->stream));
+    if (h_rgb8 && bytes && !pinned) {
+        if (h_frame_rows) {                    // pageable full frame: compact rows through the scene's pinned buffer, placed by the host in render_finish
+            if (bytes > s->pinned_cap) {
+                if (s->h_pinned) cudaFreeHost(s->h_pinned);
+                s->h_pinned = nullptr; s->pinned_cap = 0;
+                CUDA_TRY(cudaMallocHost(&s->h_pinned, bytes));
+                s->pinned_cap = bytes;
             }
+            pr->stage = s->h_pinned;
+            CUDA_TRY(cudaMemcpyAsync(pr->stage, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
+        } else {
+            CUDA_TRY(cudaMemcpyAsync(h_rgb8, s->d_frame, bytes, cudaMemcpyDeviceToHost, s->stream));
         }
-        CUDA_TRY(cudaStreamSynchronize(s->stream));
-        s->samples_pending = false;
+    }
+    return RTB_OK;
+}
+
+static int render_finish(rtb_scene* s, rtb_scene::Pending* pr, bool* redo) {
+    const TraceArgs& a = pr->a;
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+    s->samples_pending = false;
+    const int rc = validate_grids(s, redo);
+    if (rc != RTB_OK) return rc;
+    if (*redo) return RTB_OK;
+    if (pr->stage) {
+        const size_t rb = (size_t)a.width * 3;
+        for (uint32_t lr = 0; lr < a.owned_rows; ++lr) {
+            const uint32_t lb = lr / a.band_rows, within = lr - lb * a.band_rows;
+            memcpy(pr->h_rgb8 + (size_t)((lb * a.world + a.rank) * a.band_rows + within) * rb, pr->stage + (size_t)lr * rb, rb);
+        }
+    }
+    return RTB_OK;
+}
+
+static int render_core(rtb_scene* s, const rtb_render_params* p, uint8_t* h_rgb8, uint8_t* d_full, rtb_stats* stats, int first_attempt = 0) {
+    if (!s || !p) return fail(RTB_ERR_ARG, "render: null argument");
+    if (s->pend.active) return fail(RTB_ERR_STATE, "render: a frame begun with rtb_render_begin is in flight (rtb_render_end first)");
+    if (first_attempt == 0) s->grid_redo = 0;
+    uint32_t rebuilds = 0;
+    for (int attempt = first_attempt; ; ++attempt) {
+        rtb_scene::Pending pr;
+        int rc = render_enqueue(s, p, h_rgb8, d_full, attempt == 0, &pr);
+        if (rc != RTB_OK) return rc;
+        rebuilds += pr.rebuilds;
         bool redo = false;
-        rc = validate_grids(s, &redo);
+        rc = render_finish(s, &pr, &redo);
         if (rc != RTB_OK) return rc;
         if (redo && attempt == 0) { s->grid_redo++; continue; }
         if (redo) return fail(RTB_ERR_STATE, "render: grid rebuild failed twice");
-        if (stage) {
-            const size_t rb = (size_t)a.width * 3;
-            for (uint32_t lr = 0; lr < a.owned_rows; ++lr) {
-                const uint32_t lb = lr / a.band_rows, within = lr - lb * a.band_rows;
-                memcpy(h_rgb8 + (size_t)((lb * a.world + a.rank) * a.band_rows + within) * rb, stage + (size_t)lr * rb, rb);
-            }
-        }
         float ms = 0.0f;
         CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
         s->grid_rebuilds = rebuilds;
-        return fetch_stats(s, p, (uint64_t)a.owned_rows * a.width, ms, 8, stats);
+        return fetch_stats(s, p, (uint64_t)pr.a.owned_rows * pr.a.width, ms, 8, stats);
     }
+}
+
+// rtb_render in two halves.  Between them the caller may hand over the NEXT frame's sample table (rtb_scene_set_samples_async
+// with a pinned table): its upload, light tables and light grids then run next to this frame's kernels.
+int rtb_render_begin(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8) {
+    if (!s || !p || !rgb8) return fail(RTB_ERR_ARG, "rtb_render_begin: null argument");
+    if (s->pend.active) return fail(RTB_ERR_STATE, "rtb_render_begin: a frame is already in flight");
+    cudaPointerAttributes pa;
+    if (!(cudaPointerGetAttributes(&pa, rgb8) == cudaSuccess && pa.type == cudaMemoryTypeHost)) {
+        cudaGetLastError();
+        return fail(RTB_ERR_ARG, "rtb_render_begin: the frame must be page-locked host memory (the copy is asynchronous)");
+    }
+    if (p->flags & RTB_FLAG_PROFILE) return fail(RTB_ERR_ARG, "rtb_render_begin: RTB_FLAG_PROFILE needs the blocking rtb_render");
+    s->grid_redo = 0;
+    const int rc = render_enqueue(s, p, rgb8, nullptr, true, &s->pend);
+    if (rc != RTB_OK) { cudaStreamSynchronize(s->stream); return rc; }
+    s->pend.active = true;
+    return RTB_OK;
+}
+
+int rtb_render_end(rtb_scene* s, rtb_stats* stats) {
+    if (!s) return fail(RTB_ERR_ARG, "rtb_render_end: null argument");
+    if (!s->pend.active) return fail(RTB_ERR_STATE, "rtb_render_end: no frame in flight");
+    CUDA_TRY(cudaSetDevice(s->device));
+    bool redo = false;
+    int rc = render_finish(s, &s->pend, &redo);
+    s->pend.active = false;
+    if (rc != RTB_OK) return rc;
+    if (redo) {                                    // a speculative build did not fit: rebuilt with room, the frame rendered again (blocking)
+        s->grid_redo = 1;
+        const uint32_t before = s->pend.rebuilds;
+        rc = render_core(s, &s->pend.p, s->pend.h_rgb8, nullptr, stats, 1);
+        if (rc == RTB_OK) { s->grid_rebuilds += before; if (stats) stats->grid_rebuilds = s->grid_rebuilds; }
+        return rc;
+    }
+    float ms = 0.0f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+    s->grid_rebuilds = s->pend.rebuilds;
+    return fetch_stats(s, &s->pend.p, (uint64_t)s->pend.a.owned_rows * s->pend.a.width, ms, 8, stats);
 }
 
 int rtb_render(rtb_scene* s, const rtb_render_params* p, uint8_t* rgb8, rtb_stats* stats) {

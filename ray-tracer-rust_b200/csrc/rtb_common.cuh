@@ -80,6 +80,7 @@ struct GridArgs {                  // build-time arguments
     uint32_t cells_alloc;          // cell_start / cell_fill entries allocated (total cells + 1 must fit)
     uint32_t expect_big;           // big-list length the caller's kernel arguments assume
     uint64_t sat_alloc, entries_alloc;
+    uint32_t keyed;                // 1: the fill pass leaves an 8-bit coverage key above each primitive id (n_tris < 2^24); k_grid_sort orders by it
 };
 #define RTB_GRID_FAIL_CELLS 1u     // more cells than allocated
 #define RTB_GRID_FAIL_BIG 2u       // big list longer than RTB_GRID_MAX_BIG or different from the expected length
@@ -104,6 +105,10 @@ struct RtbGrid {                   // host-side owner of the light grids of one 
     // and that comes from the COUNT pass); the shadow kernels wait for ev_fill (fill_async: not waited for yet)
     cudaStream_t side; cudaEvent_t ev_count, ev_fill; bool fill_async;
     uint32_t builds, spec_builds, spec_failures;   // statistics
+    // the entries carry an 8-bit coverage key above the primitive id (readers mask it off); `sorted`: k_grid_sort has ordered the lists
+    // by it -- done when a build is used for a SECOND frame (rtb_grid_sort_on_reuse), a build per frame keeps the fill pass's two classes
+    bool keyed, sorted;
+    bool sort_at_build;            // set by the caller before a build: run k_grid_sort with it (the frame share is large enough to repay the pass at once)
 };
 
 // hit record / queue item words (rtb_trace.cu)
@@ -144,6 +149,7 @@ struct TraceArgs {
     uint32_t pool_cap;
     // light grids (rtb_grid.cu); grid_lights == nullptr: list / walk path
     const GridLight* grid_lights; const uint32_t* grid_cell_start; const int* grid_entries; const int* grid_big; uint32_t grid_n_big;
+    int grid_entry_mask, cam_entry_mask;   // primitive id = entry & mask (0xffffff when the entries carry coverage keys, else -1)
     // camera grid for primary rays (one GridLight, the eye); cam_grid == nullptr: BVH traversal
     const GridLight* cam_grid; const uint32_t* cam_cell_start; const int* cam_entries; const int* cam_big; uint32_t cam_n_big;
     const GridUnion* grid_union; const uint32_t* grid_sat;

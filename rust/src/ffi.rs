@@ -98,6 +98,8 @@ extern "C" {
                                      n_poses: u32, frames: *mut u8, png_pattern: *const c_char, stats: *mut RtbSequenceStats) -> i32;
     pub fn rtb_measure_peaks(device: i32, fp32_tflops: *mut f32, l2_read_gbs: *mut f32, hbm_read_gbs: *mut f32) -> i32;
     pub fn rtb_render(scene: *mut RtbScene, params: *const RtbRenderParams, rgb8: *mut u8, stats: *mut RtbStats) -> i32;
+    pub fn rtb_render_begin(scene: *mut RtbScene, params: *const RtbRenderParams, rgb8: *mut u8) -> i32;
+    pub fn rtb_render_end(scene: *mut RtbScene, stats: *mut RtbStats) -> i32;
     pub fn rtb_render_device(scene: *mut RtbScene, params: *const RtbRenderParams, d_rgb8: *mut c_void, cuda_stream: *mut c_void) -> i32;
     pub fn rtb_render_pixels(scene: *mut RtbScene, params: *const RtbRenderParams, pixels: *const u32, n_pix: u64,
                              rgb_lin: *mut f32, rgb8: *mut u8, hit_count: *mut u8, prim0: *mut i32, t0: *mut f32,

@@ -32,9 +32,23 @@ for world in worlds:
                 sc.set_samples_async(smp2 if i & 1 else smp)
             km.append(sc.render(out=out, **rk)[1]["kernel_ms"])
         return (time.perf_counter() - t0) / n * 1e3, float(np.mean(km))
+    def pipelined(n):
+        """begin / next table / end: the next frame's table and grids are prepared next to the frame in flight"""
+        torch.cuda.synchronize()
+        sc.set_samples_async(smp)
+        t0 = time.perf_counter(); km = []
+        for i in range(n):
+            sc.render_begin(out, **rk)
+            sc.set_samples_async(smp if i & 1 else smp2)
+            km.append(sc.render_end()[1]["kernel_ms"])
+        return (time.perf_counter() - t0) / n * 1e3, float(np.mean(km))
     loop(3, True)
     a, ka = loop(10, False)
     b, kb = loop(10, True)
+    pipelined(3)
+    c, kc = pipelined(10)
+    print("config %s world %d: pipelined (render_begin / set_samples_async / render_end) %.3f ms/step (events %.3f)" % (cfg, world, c, kc), flush=True)
+    sc.render(out=out, **rk)
     st = sc.render(out=out, **rk)[1]
     print("config %s world %d: same table %.3f ms/step (events %.3f) | new table %.3f ms/step (events %.3f) | rebuild cost %.3f ms | redo %d crc %08x"
           % (cfg, world, a, ka, b, kb, b - a, st["grid_redo"], zlib.crc32(out.tobytes()) & 0xffffffff), flush=True)

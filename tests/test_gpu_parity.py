@@ -543,6 +543,54 @@ def test_speculative_grid_rebuild_and_redo(rtb, big_bunny_inputs, monkeypatch):
             assert redo >= 2                                        # every frame after the first was rendered twice
 
 
+def test_render_begin_end_with_prefetched_tables(rtb, big_bunny_inputs, monkeypatch):
+    """rtb_render_begin / rtb_scene_set_samples_async (next table, built next to the frame in flight) / rtb_render_end: every frame
+    equals the blocking render with the same table, also when the prefetched speculative build reports that it did not fit and the
+    frame is redone inside rtb_render_end; band shares into a full host frame work the same; calls that would disturb the frame in
+    flight are refused."""
+    import torch
+    v, c, smp = big_bunny_inputs
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=2, nb_light_sample=20)
+    tables = [torch.from_numpy(t).pin_memory().numpy() for t in (smp, S.make_samples(seed=91), S.make_samples(seed=92), S.make_samples(seed=93))]
+    ref = rtb.Scene(v, c)
+    want = []
+    for t in tables:
+        ref.set_samples(t)
+        want.append(ref.render(**kw)[0].copy())
+    assert not (want[0] == want[1]).all()
+    out = [torch.empty((360, 640, 3), dtype=torch.uint8).pin_memory().numpy() for _ in range(2)]
+    for fail in (False, True):
+        if fail:
+            monkeypatch.setenv("RTB200_SPEC_FAIL", "1")
+        sc = rtb.Scene(v, c)
+        sc.set_samples_async(tables[0])
+        rebuilds = redo = 0
+        for rnd in range(2):                                        # the second round re-uses both table sets
+            for k in range(len(tables)):
+                o = out[k & 1]; o[:] = 0
+                sc.render_begin(o, **kw)
+                with pytest.raises(RuntimeError):
+                    sc.render(**kw)                                 # one frame in flight per scene
+                sc.set_samples_async(tables[(k + 1) % len(tables)])
+                got, st = sc.render_end()
+                assert (got == want[k]).all(), (fail, rnd, k)
+                rebuilds += st["grid_rebuilds"]; redo += st["grid_redo"]
+        assert rebuilds >= 8, rebuilds
+        assert (redo >= 6) if fail else (redo == 0), redo
+        # a band share (rank 1 of 2) into the full frame: the other rank's rows stay untouched
+        full = out[0]; full[:] = 7
+        sc.render_begin(full, band_rows=4, rank=1, world=2, frame_rows=True, **kw)
+        sc.set_samples_async(tables[1])
+        sc.render_end()
+        rows = np.arange(360)
+        mine = (rows // 4) % 2 == 1
+        assert (full[mine] == want[0][mine]).all() and (full[~mine] == 7).all()
+        with pytest.raises(RuntimeError):
+            sc.render_end()                                         # nothing in flight
+        # the prefetched table is what the blocking call renders next
+        assert (sc.render(**kw)[0] == want[1]).all()
+
+
 def test_render_sequence_equals_blocking_renders(rtb, gpu_big_bunny, big_bunny_inputs, tmp_path, monkeypatch):
     """rtb_render_sequence over all 120 orbit poses (BASELINE config 5, 1080p) == rtb_render per pose, byte for
     byte; PNG files written by the encoder pool decode to the same pixels; and once more with every speculative camera-grid
