@@ -307,13 +307,25 @@ __global__ void __launch_bounds__(1024) k_grid_sat_cols(uint32_t* __restrict__ s
 //      five-step search over the lanes' offsets) and lane j of a round computes the cell span [sx0, sx1] of row item j;
 //   3. every lane lists the first four cells of its own span (spans average 2.7 cells); what is left of longer spans is concatenated
 //      the same way and lane j of an emission round lists cell j of the remainder.
-#define RTB_RASTER_REC 17
+#define RTB_KEY_FRONT 197u               // keys >= this (coverage estimate >= 60 %; keys are 254 sqrt(coverage)) fill a cell's list from the front, the others from the back
+#ifndef RTB_KEY_FRONT_LONG
+#define RTB_KEY_FRONT_LONG 96u           // ... in a list too long for k_grid_sort (more than RTB_SORT_MAX entries), which has only these two classes
+#endif
+#define RTB_SORT_MAX 32
+#define RTB_RASTER_REC 18
 #define RTB_RASTER_DIRECT 4              // cells of its own span every lane lists itself
-// coverage key of cell `rel` (relative to the span start; grid column cx) of a row item: 255 = covered entirely, else the estimate
-__device__ __forceinline__ uint32_t raster_key(int rel, int cx, int c0, int c1, uint32_t hp, uint32_t kp) {
-    const int h0 = (int)(hp & 0xffffu), h1 = (int)(hp >> 16) - 1;
-    const uint32_t key = rel < h0 || rel > h1 ? 0u : (rel == h0 ? (kp >> 8) & 0xffu : (rel == h1 ? (kp >> 16) & 0xffu : kp & 0xffu));
-    return cx >= c0 && cx <= c1 ? 255u : key;
+// Coverage key of a cell (0 .. 254, 254 sqrt(share)): the estimated share of the cell the triangle's projection covers, i.e. the probability that it
+// occludes a ray that looks the cell up.  Within the row the projection is, up to the vertices inside it, the trapezoid between its
+// cross-sections I0 = [i0lo, i0hi] at the lower and I1 at the upper edge of the row (an empty one: a tip): the cell's x overlap
+// with the two, averaged, times the z overlap of row and triangle (kscale = fz / (2 cell)).  A triangle that lies within the row
+// has no cross-section at either edge: its area, spread over the cells of its span (ksmall >= 0).
+__device__ __forceinline__ uint32_t raster_key(int cx, float Gx0, float Gcell, float i0lo, float i0hi, float i1lo, float i1hi, float kscale, float ksmall) {
+    const float xa = Gx0 + (float)cx * Gcell, xb = xa + Gcell;
+    const float ov0 = fmaxf(fminf(i0hi, xb) - fmaxf(i0lo, xa), 0.0f), ov1 = fmaxf(fminf(i1hi, xb) - fmaxf(i1lo, xa), 0.0f);
+    const float cov = fminf(ksmall >= 0.0f ? ksmall : kscale * (ov0 + ov1), 1.0f);
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(cov));          // square-root scale: small coverages (many small primitives per cell) keep their order in 8 bits
+    return (uint32_t)(r * 254.0f);
 }
 // Lists U cells per lane.  Count pass: one atomic each.  Fill pass: the position comes back from an atomic, so the U of them are
 // issued together -- offsets loaded, atomics issued, then the stores -- or the pass is a chain of L2 round trips per warp.
@@ -332,7 +344,8 @@ __device__ __forceinline__ void raster_emit(const GridArgs& g, const uint32_t (&
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             old[u] = 0u;
-            front[u] = front[u] || cnt[u] >= 65536u;
+            // (front[] came in as key >= RTB_KEY_FRONT; a list too long for k_grid_sort has only these two classes: a lower bar)
+            front[u] = front[u] || cnt[u] >= 65536u || (cnt[u] > RTB_SORT_MAX && (eprim[u] >> 24) >= RTB_KEY_FRONT_LONG);
             if (ok[u]) old[u] = atomicAdd(g.cell_fill + cell[u], front[u] ? 1u : 0x10000u);
         }
 #pragma unroll
@@ -350,7 +363,6 @@ __device__ __forceinline__ void raster_emit(const GridArgs& g, const uint32_t (&
 #ifndef RTB_RASTER_RB
 #define RTB_RASTER_RB 4096               // rows of every pair dealt at a time (all: k_grid_sort decides the order of a list, not the arrival)
 #endif
-#define RTB_KEY_FRONT 153u               // keys >= this (coverage estimate >= 60 %) fill a cell's list from the front, the others from the back
 template <bool FILL>
 __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
     __shared__ float rec[RTB_RASTER_REC][256];                    // [field][thread]: lanes read distinct owners -> distinct banks
@@ -391,6 +403,7 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
             rec[12][threadIdx.x] = m;
             rec[13][threadIdx.x] = 8e-6f * (ext + (bx1 - bx0) + (bz1 - bz0)) + 1e-30f;     // eps
             rec[14][threadIdx.x] = __int_as_float(cx0); rec[15][threadIdx.x] = __int_as_float(cx1); rec[16][threadIdx.x] = __int_as_float(cz0);
+            if (FILL) rec[17][threadIdx.x] = 0.5f * fabsf((x[1] - x[0]) * (z[2] - z[0]) - (x[2] - x[0]) * (z[1] - z[0]));     // projected area
         }
     }
     __syncwarp();
@@ -408,7 +421,7 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
     // x range meets that interval are exactly the cells whose rectangle meets the triangle.  Three clipped edges per ROW instead of
     // three edge functions per CELL of the bounding box, and no cells beyond the triangle's corners.  Rounding (parameters in [0, 1]
     // to 2^-22, x to a few ulps) is covered by `eps`, itself far below the margin m that makes the rasterisation conservative.
-    // FILL also finds the cells the triangle covers entirely (both z edges of the dilated rectangle inside it) for the ordering below.
+    // FILL also takes the triangle's cross-sections at the two edges of the row, for the coverage keys (raster_key).
     for (int rb = 0; rb < R; rb += 32) {
         const int ri = rb + (int)lane;
         int own = 0, own_ex = 0;                                  // the last lane whose offset is <= ri (it has rows)
@@ -418,8 +431,10 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
             if (v <= ri) { own += step; own_ex = v; }
         }
         const uint32_t olight = __shfl_sync(FULL, light, own), oprim = __shfl_sync(FULL, prim, own);
-        int sx0 = 0, len = 0, cov0 = 1, cov1 = 0;
-        uint32_t row = 0, hpack = 0xffffu, kpack = 0u;             // hpack: first | last << 16 cell (relative to sx0) the triangle's own x range reaches
+        int sx0 = 0, len = 0;
+        uint32_t row = 0;
+        float i0lo = inf, i0hi = -inf, i1lo = inf, i1hi = -inf;      // x range of the triangle AT z = Z0 and AT z = Z1 (FILL: raster_key)
+        float kscale = 0.0f, ksmall = -1.0f, kx0 = 0.0f, kcell = 0.0f;
         if (ri < R) {
             const unsigned o = wbase + (unsigned)own;
             const GridLight* __restrict__ GL = g.lights + olight;
@@ -429,7 +444,6 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
             const int cx0 = __float_as_int(rec[14][o]), cx1 = __float_as_int(rec[15][o]), cz = __float_as_int(rec[16][o]) + r0 + (ri - own_ex);
             const float Z0 = Gz0 + cz * Gcell - m - eps, Z1 = Gz0 + (cz + 1) * Gcell + m + eps;
             float X0 = inf, X1 = -inf;                               // x range of the triangle within the slab
-            float i0lo = inf, i0hi = -inf, i1lo = inf, i1hi = -inf;  // x range of the triangle AT z = Z0 and AT z = Z1 (FILL)
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 const float xa = rec[k][o], za = rec[3 + k][o], dx = rec[6 + k][o], idz = rec[9 + k][o];
@@ -453,30 +467,12 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
                 len = max(sx1 - sx0 + 1, 0);
                 row = GL->cell_base + (uint32_t)cz * (uint32_t)Gnx;
                 if (FILL) {
-                    // covered cells: the dilated x range [x0 + cx cell - m, x0 + (cx + 1) cell + m] within [in_lo, in_hi], as a cell range
-                    const float in_lo = fmaxf(i0lo, i1lo) + eps, in_hi = fminf(i0hi, i1hi) - eps;
-                    if (in_lo <= in_hi) {
-                        const float nxf = (float)Gnx;
-                        cov0 = (int)fminf(fmaxf(ceilf((in_lo + m - Gx0) * Ginv), 0.0f), nxf);
-                        cov1 = (int)fminf(fmaxf(floorf((in_hi - m - Gx0) * Ginv), 0.0f), nxf) - 1;
-                    }
-                    // Coverage estimate of the other cells, the key k_grid_sort orders a cell's list by: (x overlap of the cell with
-                    // the triangle's x range in this row) x (z overlap of the row with the triangle's z range), as a fraction of the
-                    // cell, in 1/254ths.  Cells between the first and the last the range reaches overlap fully in x; cells the span
-                    // holds only because of the dilation get 0.
                     const float bz0 = fminf(fminf(rec[3][o], rec[4][o]), rec[5][o]), bz1 = fmaxf(fmaxf(rec[3][o], rec[4][o]), rec[5][o]);
                     const float rz0 = Gz0 + cz * Gcell;
                     const float fz = fminf(fmaxf((fminf(bz1, rz0 + Gcell) - fmaxf(bz0, rz0)) * Ginv, 0.0f), 1.0f);
-                    const float Xa = fmaxf(X0, Gx0), Xb = fminf(X1, Gx0 + (float)Gnx * Gcell);
-                    if (Xa <= Xb) {
-                        const int h0 = (int)floorf((Xa - Gx0) * Ginv), h1 = (int)floorf((Xb - Gx0) * Ginv);
-                        const float f0 = fminf(fmaxf((fminf(Xb, Gx0 + (float)(h0 + 1) * Gcell) - Xa) * Ginv, 0.0f), 1.0f);
-                        const float f1 = fminf(fmaxf((Xb - fmaxf(Xa, Gx0 + (float)h1 * Gcell)) * Ginv, 0.0f), 1.0f);
-                        const uint32_t km = (uint32_t)(fz * 254.0f), k0 = (uint32_t)(f0 * fz * 254.0f), k1 = (uint32_t)(f1 * fz * 254.0f);
-                        kpack = km | (k0 << 8) | (k1 << 16);
-                        const int r0 = min(max(h0 - sx0, 0), 0xffff), r1 = min(max(h1 - sx0, -1) + 1, 0xffff);      // r1: last + 1 (0 = none)
-                        hpack = (uint32_t)r0 | ((uint32_t)r1 << 16);
-                    }
+                    kscale = fz * 0.5f * Ginv; kx0 = Gx0; kcell = Gcell;
+                    if (!(i0lo <= i0hi) && !(i1lo <= i1hi))
+                        ksmall = fminf(rec[17][o] * Ginv * Ginv, 1.0f) / (float)max(len, 1);
                 }
             }
         }
@@ -492,7 +488,7 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
                 cell[u] = row + (uint32_t)(sx0 + u);
                 eprim[u] = oprim; front[u] = false;
                 if (FILL) {
-                    const uint32_t key = raster_key(u, sx0 + u, cov0, cov1, hpack, kpack);
+                    const uint32_t key = raster_key(sx0 + u, kx0, kcell, i0lo, i0hi, i1lo, i1hi, kscale, ksmall);
                     front[u] = key >= RTB_KEY_FRONT;
                     if (g.keyed) eprim[u] |= key << 24;
                 }
@@ -525,9 +521,8 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
                 eprim[u] = 0u; front[u] = false;
                 if (FILL) {
                     eprim[u] = __shfl_sync(FULL, oprim, so);
-                    const int c0 = __shfl_sync(FULL, cov0, so), c1 = __shfl_sync(FULL, cov1, so);
-                    const uint32_t hp = __shfl_sync(FULL, hpack, so), kp = __shfl_sync(FULL, kpack, so);
-                    const uint32_t key = raster_key(rel, cx, c0, c1, hp, kp);
+                    const uint32_t key = raster_key(cx, __shfl_sync(FULL, kx0, so), __shfl_sync(FULL, kcell, so), __shfl_sync(FULL, i0lo, so), __shfl_sync(FULL, i0hi, so),
+                                                    __shfl_sync(FULL, i1lo, so), __shfl_sync(FULL, i1hi, so), __shfl_sync(FULL, kscale, so), __shfl_sync(FULL, ksmall, so));
                     front[u] = key >= RTB_KEY_FRONT;
                     if (g.keyed) eprim[u] |= key << 24;
                 }
@@ -550,7 +545,6 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
 // large enough to repay it at once (RtbGrid::sort_at_build: 48 Mi rays or more), else when a build is used for a SECOND frame
 // (rtb_grid_sort_on_reuse): a band share of 8 GPUs that draws a new table per frame keeps the two classes, a caller that reuses
 // the table (or the camera) gets the full order from the second frame on.  The keys stay in the entries; readers mask them off.
-#define RTB_SORT_MAX 32
 __device__ __forceinline__ void sort_ce(uint32_t& a, uint32_t& b) { const uint32_t hi = max(a, b), lo = min(a, b); a = hi; b = lo; }
 __global__ void __launch_bounds__(256) k_grid_sort(GridArgs g) {
     if (g.ctl[4]) return;                                          // a build that did not fit: the grids are off, the offsets mean nothing
