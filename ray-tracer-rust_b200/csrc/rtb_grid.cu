@@ -307,25 +307,35 @@ __global__ void __launch_bounds__(1024) k_grid_sat_cols(uint32_t* __restrict__ s
 //      five-step search over the lanes' offsets) and lane j of a round computes the cell span [sx0, sx1] of row item j;
 //   3. every lane lists the first four cells of its own span (spans average 2.7 cells); what is left of longer spans is concatenated
 //      the same way and lane j of an emission round lists cell j of the remainder.
-#define RTB_KEY_FRONT 197u               // keys >= this (coverage estimate >= 60 %; keys are 254 sqrt(coverage)) fill a cell's list from the front, the others from the back
+#ifndef RTB_KEY_DEPTH
+#define RTB_KEY_DEPTH 1
+#endif
+#define RTB_KEY_FRONT 127u               // keys >= this (coverage estimate >= 60 %, raster_key) fill a cell's list from the front, the others from the back
 #ifndef RTB_KEY_FRONT_LONG
-#define RTB_KEY_FRONT_LONG 96u           // ... in a list too long for k_grid_sort (more than RTB_SORT_MAX entries), which has only these two classes
+#define RTB_KEY_FRONT_LONG 62u           // ... in a list too long for k_grid_sort (more than RTB_SORT_MAX entries), which has only these two classes
 #endif
 #define RTB_SORT_MAX 32
-#define RTB_RASTER_REC 18
+#define RTB_RASTER_REC 19
 #define RTB_RASTER_DIRECT 4              // cells of its own span every lane lists itself
-// Coverage key of a cell (0 .. 254, 254 sqrt(share)): the estimated share of the cell the triangle's projection covers, i.e. the probability that it
+// Coverage key of a cell: from the estimated share of the cell the triangle's projection covers, i.e. the probability that it
 // occludes a ray that looks the cell up.  Within the row the projection is, up to the vertices inside it, the trapezoid between its
 // cross-sections I0 = [i0lo, i0hi] at the lower and I1 at the upper edge of the row (an empty one: a tip): the cell's x overlap
 // with the two, averaged, times the z overlap of row and triangle (kscale = fz / (2 cell)).  A triangle that lies within the row
 // has no cross-section at either edge: its area, spread over the cells of its span (ksmall >= 0).
-__device__ __forceinline__ uint32_t raster_key(int cx, float Gx0, float Gcell, float i0lo, float i0hi, float i1lo, float i1hi, float kscale, float ksmall) {
+// Keys 128 .. 254: the estimate is 60 % or more -- such a primitive occludes nearly every ray from BELOW it that looks the cell up,
+// and what decides is whether the ray starts below it: the nearer to the light point, the more hit points it shadows (a hit point
+// on the far side of the bunny is occluded by the near side's primitive of its cell, never by its own neighbours).  These are
+// ordered by height above the plane (depth7, 0 .. 126 = at the light point).  Keys 0 .. 127: 127 sqrt(share / 0.6).
+__device__ __forceinline__ uint32_t raster_key(int cx, float Gx0, float Gcell, float i0lo, float i0hi, float i1lo, float i1hi, float kscale, float ksmall, uint32_t depth7) {
     const float xa = Gx0 + (float)cx * Gcell, xb = xa + Gcell;
     const float ov0 = fmaxf(fminf(i0hi, xb) - fmaxf(i0lo, xa), 0.0f), ov1 = fmaxf(fminf(i1hi, xb) - fmaxf(i1lo, xa), 0.0f);
-    const float cov = fminf(ksmall >= 0.0f ? ksmall : kscale * (ov0 + ov1), 1.0f);
+    const float cov = ksmall >= 0.0f ? ksmall : kscale * (ov0 + ov1);
+#if RTB_KEY_DEPTH
+    if (cov >= 0.6f) return 128u + depth7;
+#endif
     float r;
-    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(cov));          // square-root scale: small coverages (many small primitives per cell) keep their order in 8 bits
-    return (uint32_t)(r * 254.0f);
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fminf(cov * (1.0f / 0.6f), 1.0f)));   // square-root scale: small shares (many small primitives per cell) keep their order
+    return (uint32_t)(r * 127.0f);
 }
 // Lists U cells per lane.  Count pass: one atomic each.  Fill pass: the position comes back from an atomic, so the U of them are
 // issued together -- offsets loaded, atomics issued, then the stores -- or the pass is a chain of L2 round trips per warp.
@@ -403,7 +413,11 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
             rec[12][threadIdx.x] = m;
             rec[13][threadIdx.x] = 8e-6f * (ext + (bx1 - bx0) + (bz1 - bz0)) + 1e-30f;     // eps
             rec[14][threadIdx.x] = __int_as_float(cx0); rec[15][threadIdx.x] = __int_as_float(cx1); rec[16][threadIdx.x] = __int_as_float(cz0);
-            if (FILL) rec[17][threadIdx.x] = 0.5f * fabsf((x[1] - x[0]) * (z[2] - z[0]) - (x[2] - x[0]) * (z[1] - z[0]));     // projected area
+            if (FILL) {
+                rec[17][threadIdx.x] = 0.5f * fabsf((x[1] - x[0]) * (z[2] - z[0]) - (x[2] - x[0]) * (z[1] - z[0]));     // projected area
+                const float up = (fmaxf(fmaxf(q0.y, q1.y), q2.y) - g.y_plane) / G.H;                                      // height above the plane, 1 = at the light point
+                rec[18][threadIdx.x] = __uint_as_float((uint32_t)(fminf(fmaxf(up, 0.0f), 1.0f) * 126.0f));
+            }
         }
     }
     __syncwarp();
@@ -435,6 +449,7 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
         uint32_t row = 0;
         float i0lo = inf, i0hi = -inf, i1lo = inf, i1hi = -inf;      // x range of the triangle AT z = Z0 and AT z = Z1 (FILL: raster_key)
         float kscale = 0.0f, ksmall = -1.0f, kx0 = 0.0f, kcell = 0.0f;
+        uint32_t kdepth = 0u;
         if (ri < R) {
             const unsigned o = wbase + (unsigned)own;
             const GridLight* __restrict__ GL = g.lights + olight;
@@ -470,7 +485,7 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
                     const float bz0 = fminf(fminf(rec[3][o], rec[4][o]), rec[5][o]), bz1 = fmaxf(fmaxf(rec[3][o], rec[4][o]), rec[5][o]);
                     const float rz0 = Gz0 + cz * Gcell;
                     const float fz = fminf(fmaxf((fminf(bz1, rz0 + Gcell) - fmaxf(bz0, rz0)) * Ginv, 0.0f), 1.0f);
-                    kscale = fz * 0.5f * Ginv; kx0 = Gx0; kcell = Gcell;
+                    kscale = fz * 0.5f * Ginv; kx0 = Gx0; kcell = Gcell; kdepth = __float_as_uint(rec[18][o]);
                     if (!(i0lo <= i0hi) && !(i1lo <= i1hi))
                         ksmall = fminf(rec[17][o] * Ginv * Ginv, 1.0f) / (float)max(len, 1);
                 }
@@ -488,8 +503,8 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
                 cell[u] = row + (uint32_t)(sx0 + u);
                 eprim[u] = oprim; front[u] = false;
                 if (FILL) {
-                    const uint32_t key = raster_key(sx0 + u, kx0, kcell, i0lo, i0hi, i1lo, i1hi, kscale, ksmall);
-                    front[u] = key >= RTB_KEY_FRONT;
+                    const uint32_t key = raster_key(sx0 + u, kx0, kcell, i0lo, i0hi, i1lo, i1hi, kscale, ksmall, kdepth);
+                    front[u] = key > RTB_KEY_FRONT;
                     if (g.keyed) eprim[u] |= key << 24;
                 }
             }
@@ -522,8 +537,8 @@ __global__ void __launch_bounds__(256) k_grid_raster(GridArgs g) {
                 if (FILL) {
                     eprim[u] = __shfl_sync(FULL, oprim, so);
                     const uint32_t key = raster_key(cx, __shfl_sync(FULL, kx0, so), __shfl_sync(FULL, kcell, so), __shfl_sync(FULL, i0lo, so), __shfl_sync(FULL, i0hi, so),
-                                                    __shfl_sync(FULL, i1lo, so), __shfl_sync(FULL, i1hi, so), __shfl_sync(FULL, kscale, so), __shfl_sync(FULL, ksmall, so));
-                    front[u] = key >= RTB_KEY_FRONT;
+                                                    __shfl_sync(FULL, i1lo, so), __shfl_sync(FULL, i1hi, so), __shfl_sync(FULL, kscale, so), __shfl_sync(FULL, ksmall, so), __shfl_sync(FULL, kdepth, so));
+                    front[u] = key > RTB_KEY_FRONT;
                     if (g.keyed) eprim[u] |= key << 24;
                 }
             }
