@@ -102,6 +102,7 @@ struct rtb_scene {
     // the rest on `copy_stream`; renders make their stream wait for ev_prefix / ev_samples where they need the data
     cudaStream_t copy_stream; cudaEvent_t ev_prefix, ev_samples, ev_idle; bool samples_pending; uint32_t samples_prefix;
     uint32_t grid_rebuilds, grid_redo;           // grid builds enqueued / redone by the last blocking render
+    bool no_refine;                              // RTB200_NO_REFINE: never rebuild the light grids finer for a table that keeps being reused
     // rtb_render_multi with RTB_FLAG_GATHER_PEER: the full frame on this device, written by every device of the call
     uint8_t* d_full; size_t full_cap;
     // rtb_render_sequence: two device frames, two pinned host frames, snapshots of the camera grid's control words
@@ -289,6 +290,7 @@ int rtb_scene_create_ex(const rtb_scene_desc* desc, const rtb_scene_options* opt
     TRY_(cudaEventCreateWithFlags(&s->ev_prefix, cudaEventDisableTiming));
     TRY_(cudaEventCreateWithFlags(&s->ev_samples, cudaEventDisableTiming));
     TRY_(cudaEventCreateWithFlags(&s->ev_idle, cudaEventDisableTiming));
+    s->no_refine = getenv("RTB200_NO_REFINE") != nullptr;
     if (const char* env = getenv("RTB200_GRID_CELL")) { const float v = (float)atof(env); if (v > 0.0f) s->grid_cell_factor = v; }
     TRY_(cudaMalloc(&s->d_counters, RTB_NUM_CTRS * sizeof(unsigned long long)));
     TRY_(cudaMalloc(&s->d_light_box, 8 * sizeof(float)));
@@ -460,8 +462,26 @@ static int build_tables(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         CUDA_TRY(rtb_grid_build(s->grid, s->d_tris, s->n_tris, s->d_light_pts, (uint32_t)need, s->grid_cell_factor, allow_spec, st));
         s->grid_rebuilds++;
         s->grid.key_set = true; s->grid.key_samples = s->samples_version; s->grid.key_n_lights = (uint32_t)need;
+        s->grid.uses = 0; s->grid.refined = false;
     } else if (s->shadow_mode != 1 && p->nb_ray && p->nb_light_sample) {
-        CUDA_TRY(rtb_grid_sort_on_reuse(s->grid, st));             // the second frame of a table: the lists get their full order
+        // The table is being reused.  A build is sized for a caller that draws a new table per frame (the reference, src/main.rs:
+        // 260-265): cells of 0.25 mean primitive extents, lists in two classes -- rebuilding costs about a millisecond per frame.  Smaller
+        // cells and fully ordered lists make every later frame faster (4K / 16 spp: 15.6 -> 14.5 ms at 0.1 extents, distance 576:
+        // 38.0 -> 33.6 ms) but cost 3 - 6 times the build: the second frame of a table orders the lists, the third rebuilds finer.
+        s->grid.uses++;
+        if (s->grid.uses == 2 && !s->grid.refined && !s->no_refine && s->grid.valid) {
+            s->grid.sort_at_build = true;
+            CUDA_TRY(rtb_grid_build(s->grid, s->d_tris, s->n_tris, s->d_light_pts, (uint32_t)need, s->grid_cell_factor * 0.4f, false, st));
+            s->grid_rebuilds++;
+            s->grid.refined = true;
+            if (!s->grid.valid) {                  // the finer grids did not fit: back to the build the first frames used
+                s->grid.sort_at_build = true;
+                CUDA_TRY(rtb_grid_build(s->grid, s->d_tris, s->n_tris, s->d_light_pts, (uint32_t)need, s->grid_cell_factor, false, st));
+                s->grid_rebuilds++;
+            }
+        } else {
+            CUDA_TRY(rtb_grid_sort_on_reuse(s->grid, st));
+        }
     }
     ti->need = need; ti->n_groups = n_groups; ti->group_size = group_size; ti->use_perm = use_perm;
     return RTB_OK;

@@ -98,6 +98,8 @@ struct RtbGrid {                   // host-side owner of the light grids of one 
     uint64_t key_samples; uint32_t key_n_lights; bool key_set;
     // speculative rebuilds (rtb_grid.cu: grid_build_ex): state of the last synchronous build and of a pending speculative one
     bool spec_ok; uint32_t spec_n_tris, spec_n_big_; float spec_cell0, spec_y_plane; bool spec_with_union;
+    uint32_t spec_cells;           // cells of that build: a speculative build scans (and checks itself against) 1.25 x this, not the whole allocation
+    float spec_req;                // the cell size the last synchronous build was ASKED for (spec_cell0: what it settled on)
     bool pending;                  // a speculative build has been enqueued and not validated yet (rtb_grid_validate)
     uint64_t entry_cap_limit;      // entries above which the grid path is not taken (0 = default 512 Mi); tests lower it
     cudaEvent_t ev0, ev1;          // build time
@@ -108,6 +110,9 @@ struct RtbGrid {                   // host-side owner of the light grids of one 
     // the entries carry an 8-bit coverage key above the primitive id (readers mask it off); `sorted`: k_grid_sort has ordered the lists
     // by it -- done when a build is used for a SECOND frame (rtb_grid_sort_on_reuse), a build per frame keeps the fill pass's two classes
     bool keyed, sorted;
+    // frames rendered with this build after the first (the caller counts); `refined`: rebuilt with finer cells because the table keeps
+    // being reused (rtb_api.cu: build_tables)
+    uint32_t uses; bool refined;
     bool sort_at_build;            // set by the caller before a build: run k_grid_sort with it (the frame share is large enough to repay the pass at once)
 };
 

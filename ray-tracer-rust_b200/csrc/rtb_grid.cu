@@ -1056,12 +1056,16 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     G.builds++;
 
     // ---- speculative form -------------------------------------------------------------------------------------------------
-    const bool spec = allow_spec && G.spec_ok && G.spec_n_tris == n_tris && G.spec_with_union == with_union && G.spec_y_plane == y_plane &&
+    const bool spec = allow_spec && G.spec_ok && G.spec_n_tris == n_tris && G.spec_with_union == with_union && G.spec_y_plane == y_plane && G.spec_req == cell0 &&
                       G.cell_start_cap > 1 && G.entries_cap > 1 && (!with_union || G.sat_cap > 0);
     if (spec) {
         g.cell0 = G.spec_cell0;
         const bool force_fail = getenv("RTB200_SPEC_FAIL") != nullptr;             // tests: every speculative build "does not fit"
-        g.speculative = 1u; g.cells_alloc = force_fail ? 1u : (uint32_t)G.cell_start_cap; g.expect_big = G.n_big = G.spec_n_big_;
+        // the arrays may be far larger than this shape needs (a finer build for a reused table came before): the passes below run over
+        // `nc` cells, the capacity a build of this shape was given, and the device-side check is against the same number
+        size_t nc = (size_t)G.spec_cells + (size_t)G.spec_cells / 4 + 1024;
+        if (nc > G.cell_start_cap) nc = G.cell_start_cap;
+        g.speculative = 1u; g.cells_alloc = force_fail ? 1u : (uint32_t)nc; g.expect_big = G.n_big = G.spec_n_big_;
         g.sat_alloc = G.sat_cap; g.entries_alloc = G.entries_cap < ENTRY_CAP ? G.entries_cap : ENTRY_CAP;
         g.cell_start = G.d_cell_start; g.cell_fill = G.d_cell_fill; g.entries = G.d_entries; g.sat = G.d_sat;
         GRID_CK(cudaEventRecord(G.ev0, st));
@@ -1069,7 +1073,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
         k_grid_classify<<<(unsigned)((work + RTB_CLASSIFY_THREADS - 1) / RTB_CLASSIFY_THREADS), RTB_CLASSIFY_THREADS, 0, st>>>(g);
         k_grid_biglist<<<(n_tris + 255) / 256, 256, 0, st>>>(g);
         k_grid_layout<<<1, 1024, 0, st>>>(g);
-        const size_t nc = G.cell_start_cap;                       // scan the whole allocation: cells beyond the total hold zero counts
+        // (the scan covers all nc cells: those beyond the total hold zero counts)
         GRID_CK(cudaMemsetAsync(G.d_cell_fill, 0, nc * sizeof(uint32_t), st));
         k_grid_raster<false><<<gr, 256, 0, st>>>(g);
         size_t need = 0;
@@ -1174,7 +1178,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     GRID_CK(cudaEventSynchronize(G.ev1));
     GRID_CK(cudaEventElapsedTime(&G.build_ms, G.ev0, G.ev1));
     G.valid = true;
-    G.spec_ok = true; G.spec_n_tris = n_tris; G.spec_cell0 = g.cell0; G.spec_y_plane = y_plane; G.spec_with_union = with_union; G.spec_n_big_ = G.n_big;
+    G.spec_ok = true; G.spec_n_tris = n_tris; G.spec_cell0 = g.cell0; G.spec_req = cell0; G.spec_cells = G.total_cells + 1; G.spec_y_plane = y_plane; G.spec_with_union = with_union; G.spec_n_big_ = G.n_big;
     return cudaSuccess;
 }
 

@@ -43,7 +43,9 @@ for world in worlds:
             km.append(sc.render_end()[1]["kernel_ms"])
         return (time.perf_counter() - t0) / n * 1e3, float(np.mean(km))
     loop(3, True)
+    loop(4, False)                                   # (the third frame of a table rebuilds its grids finer, once)
     a, ka = loop(10, False)
+    loop(3, True)                                    # (the first new table after that is built synchronously, once)
     b, kb = loop(10, True)
     pipelined(3)
     c, kc = pipelined(10)

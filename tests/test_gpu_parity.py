@@ -543,6 +543,28 @@ def test_speculative_grid_rebuild_and_redo(rtb, big_bunny_inputs, monkeypatch):
             assert redo >= 2                                        # every frame after the first was rendered twice
 
 
+def test_light_grids_ordered_then_refined_for_a_reused_table(rtb, big_bunny_inputs, monkeypatch):
+    """A table that keeps being used gets its cell lists fully ordered on the second frame and finer light grids on the third
+    (rtb_api.cu: build_tables); the frames do not change by a bit, and a new table starts over with the quick build."""
+    v, c, smp = big_bunny_inputs
+    kw = dict(width=640, height=360, distance=96.0, nb_ray=2, nb_light_sample=20)
+    sc = rtb.Scene(v, c)
+    for t in (smp, S.make_samples(seed=123)):
+        sc.set_samples(t)
+        frames, rebuilds, cells = [], [], []
+        for k in range(5):
+            img, st = sc.render(**kw)
+            frames.append(img.copy()); rebuilds.append(st["grid_rebuilds"]); cells.append(st["grid_cells"])
+        assert all((f == frames[0]).all() for f in frames[1:])
+        assert rebuilds[0] >= 1 and rebuilds[1] == 0 and rebuilds[2] == 1 and rebuilds[3] == 0 and rebuilds[4] == 0, rebuilds
+        assert cells[2] > 3 * cells[0] and cells[4] == cells[2], cells                 # 0.25 -> 0.1 extents: 6.25 x the cells
+    monkeypatch.setenv("RTB200_NO_REFINE", "1")
+    sc2 = rtb.Scene(v, c); sc2.set_samples(S.make_samples(seed=123))
+    for k in range(4):
+        img, st = sc2.render(**kw)
+        assert (img == frames[0]).all() and (k == 0 or st["grid_rebuilds"] == 0)
+
+
 def test_render_begin_end_with_prefetched_tables(rtb, big_bunny_inputs, monkeypatch):
     """rtb_render_begin / rtb_scene_set_samples_async (next table, built next to the frame in flight) / rtb_render_end: every frame
     equals the blocking render with the same table, also when the prefetched speculative build reports that it did not fit and the
