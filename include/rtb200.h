@@ -311,6 +311,22 @@ typedef struct {
 int rtb_import_obj_parallel(const char* path, uint32_t n_threads, uint32_t flags, float** verts_out, uint32_t* n_out, rtb_import_stats* stats);
 void rtb_free_pinned(void* p);
 
+/* --- the Sphere primitive and the random scene generators, dead code in the reference (src/tracer/primitives/sphere.rs is
+ *     complete, but main() builds triangle scenes only; gen_random_spheres / gen_random_triangles, src/main.rs:43-99, are
+ *     #[allow(dead_code)]).  Kept at the same level here: exact pieces with a batch entry, not wired into the frame kernels.
+ * rtb_spheres_closest_hit: per ray (origin, direction: n_rays * 3 floats each, HOST; the direction is normalised as Ray::new does) the
+ *     closest of n_spheres spheres {x, y, z, radius}: idx_out (-1 = none; an exact tie goes to the later sphere), t_out = the distance
+ *     Intersectable::intersect returns (sphere.rs:50-84), normal_out = HasNormal::get_normal at origin + t * direction (sphere.rs:90-94).
+ *     Bit-exact with the oracle's restatement (tests/test_gpu_parity.py).
+ * rtb_spheres_bounds: HasBoundingBox (sphere.rs:31-43), on the host.
+ * rtb_gen_random_spheres / _triangles: the generators' shapes and ranges from an explicit seed (the reference draws from an OS-seeded
+ *     RNG): 1 sphere (4 + 3 floats) / 10 triangles (90 + 30 floats); return the primitive count. */
+int rtb_spheres_closest_hit(int32_t device, const float* spheres_xyzr, uint32_t n_spheres, const float* origins, const float* dirs,
+                            uint64_t n_rays, float* t_out, int32_t* idx_out, float* normal_out);
+void rtb_spheres_bounds(const float* spheres_xyzr, uint32_t n, float* boxes6_out);
+uint32_t rtb_gen_random_spheres(uint64_t seed, float* spheres_xyzr_out, float* colors_out);
+uint32_t rtb_gen_random_triangles(uint64_t seed, float* verts_out, float* colors_out);
+
 /* Deterministic stand-in for thread_rng (src/main.rs:260-265): SplitMix64(seed) stream, value j =
  * top 24 bits * 2^-24; out holds 2*n_pairs floats. */
 void rtb_fill_samples(uint64_t seed, uint32_t n_pairs, float* out);

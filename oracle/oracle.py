@@ -60,6 +60,10 @@ def lib():
         L.orc_primary_ray.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
         L.orc_gamma_u8.restype = C.c_uint8
         L.orc_gamma_u8.argtypes = [C.c_float]
+        L.orc_sphere_intersect.argtypes = [C.c_void_p, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_sphere_box.argtypes = [C.c_void_p, C.c_float, C.c_void_p]; L.orc_sphere_box.restype = None
+        L.orc_sphere_normal.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]; L.orc_sphere_normal.restype = None
+        L.orc_spheres_closest.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_render.restype = C.c_int32
         L.orc_render.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64] + [C.c_void_p] * 6
         _lib = L
@@ -177,3 +181,35 @@ def tri_intersect(v, o, d):
 
 def gamma_u8(c):
     return int(lib().orc_gamma_u8(float(np.float32(c))))
+
+
+# ---- the Sphere primitive (src/tracer/primitives/sphere.rs) ----
+def sphere_intersect(center, radius, o, d):
+    t = C.c_float(0)
+    ok = lib().orc_sphere_intersect(_ptr(_f32(center)), float(np.float32(radius)), _ptr(_f32(o)), _ptr(_f32(d)), C.byref(t))
+    return (t.value if ok else None)
+
+
+def sphere_box(center, radius):
+    out = np.zeros(6, np.float32)
+    lib().orc_sphere_box(_ptr(_f32(center)), float(np.float32(radius)), _ptr(out))
+    return out
+
+
+def sphere_normal(center, p):
+    out = np.zeros(3, np.float32)
+    lib().orc_sphere_normal(_ptr(_f32(center)), _ptr(_f32(p)), _ptr(out))
+    return out
+
+
+def spheres_closest(xyzr, origins, dirs):
+    """closest sphere per ray -> (idx int32 [-1 = none], t float32, normal float32[n,3])"""
+    xyzr = np.ascontiguousarray(xyzr, np.float32).reshape(-1, 4)
+    o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3); d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+    idx = np.full(len(o), -1, np.int32); t = np.zeros(len(o), np.float32); nrm = np.zeros((len(o), 3), np.float32)
+    L = lib()
+    for k in range(len(o)):
+        tk = C.c_float(0)
+        idx[k] = L.orc_spheres_closest(_ptr(xyzr), len(xyzr), _ptr(o[k]), _ptr(d[k]), C.byref(tk), _ptr(nrm[k]))
+        t[k] = tk.value
+    return idx, t, nrm

@@ -63,6 +63,26 @@ struct Ray { V3 o, d; };
 // src/tracer/utils/ray.rs:12-17 -- the constructor normalises the direction.
 inline Ray make_ray(V3 o, V3 dir) { Ray r; r.o = o; r.d = normalize(dir); return r; }
 
+// src/tracer/primitives/sphere.rs:50-84 (Intersectable for Sphere; dead code in the reference's main: SURVEY 8f-4)
+inline bool sphere_intersect(V3 center, float radius, const Ray& ray, float* t_out) {
+    const float radius2 = radius * radius;           // sphere.rs:27
+    const V3 l = sub(center, ray.o);                 // :53
+    const float tca = dot(l, ray.d);                 // :54
+    if (tca < 0.0f) return false;                    // :55-57
+    const float d2 = dot(l, l) - tca * tca;          // :58
+    if (d2 > radius2) return false;                  // :59-61
+    const float thc = sqrtf(radius2 - d2);           // :63
+    float t0 = tca - thc, t1 = tca + thc;            // :65-66
+    if (t0 > t1) { const float t = t0; t0 = t1; t1 = t; }   // :68-70
+    if (t0 < 0.0f) {                                 // :73-78
+        t0 = t1;
+        if (t0 < 0.0f) return false;
+    }
+    const V3 p_hit = add(ray.o, scale(t0, ray.d));   // :80
+    *t_out = distance(p_hit, ray.o);                 // :81
+    return true;
+}
+
 struct Box { V3 mn, mx; };
 
 struct Tri {
@@ -613,6 +633,40 @@ int32_t orc_render(const orc_scene* sc, const orc_params* prm, const uint32_t* p
         stats->seconds = secs; stats->threads = nt;
     }
     return 0;
+}
+
+// ---- the Sphere primitive (sphere.rs), piecewise ----
+// dir is normalised as Ray::new does (ray.rs:12-17); returns 1 and *t on a hit
+int orc_sphere_intersect(const float* center, float radius, const float* o, const float* dir, float* t) {
+    const Ray r = make_ray(v3(o[0], o[1], o[2]), v3(dir[0], dir[1], dir[2]));
+    return sphere_intersect(v3(center[0], center[1], center[2]), radius, r, t) ? 1 : 0;
+}
+// sphere.rs:31-43
+void orc_sphere_box(const float* c, float radius, float* out6) {
+    out6[0] = c[0] - radius; out6[1] = c[1] - radius; out6[2] = c[2] - radius;
+    out6[3] = c[0] + radius; out6[4] = c[1] + radius; out6[5] = c[2] + radius;
+}
+// sphere.rs:90-94
+void orc_sphere_normal(const float* c, const float* p, float* out3) {
+    const V3 n = normalize(sub(v3(p[0], p[1], p[2]), v3(c[0], c[1], c[2])));
+    out3[0] = n.x; out3[1] = n.y; out3[2] = n.z;
+}
+// closest sphere of a list for one ray (the rule of the triangle path: smaller distance wins, an exact tie goes to the later
+// primitive); the hit point is origin + t * direction as render_pixel forms it (src/main.rs:190), the normal sphere.rs:90-94
+int orc_spheres_closest(const float* xyzr, int32_t n, const float* o, const float* dir, float* t_out, float* normal_out) {
+    const Ray r = make_ray(v3(o[0], o[1], o[2]), v3(dir[0], dir[1], dir[2]));
+    int best = -1; float bt = 0.0f;
+    for (int i = 0; i < n; ++i) {
+        float t;
+        if (!sphere_intersect(v3(xyzr[4 * i], xyzr[4 * i + 1], xyzr[4 * i + 2]), xyzr[4 * i + 3], r, &t)) continue;
+        if (best < 0 || t < bt || t == bt) { best = i; bt = t; }
+    }
+    if (best >= 0) {
+        const V3 p = add(r.o, scale(bt, r.d));
+        const V3 nn = normalize(sub(p, v3(xyzr[4 * best], xyzr[4 * best + 1], xyzr[4 * best + 2])));
+        *t_out = bt; normal_out[0] = nn.x; normal_out[1] = nn.y; normal_out[2] = nn.z;
+    }
+    return best;
 }
 
 }  // extern "C"

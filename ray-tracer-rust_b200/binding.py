@@ -77,7 +77,7 @@ class SequenceStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
-EXPORTS = ["rtb_import_obj_parallel", "rtb_free_pinned", "rtb_color_to_u8_static", "rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
+EXPORTS = ["rtb_spheres_closest_hit", "rtb_spheres_bounds", "rtb_gen_random_spheres", "rtb_gen_random_triangles", "rtb_import_obj_parallel", "rtb_free_pinned", "rtb_color_to_u8_static", "rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
            "rtb_render_sequence", "rtb_render_sequence_multi", "rtb_measure_peaks", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render", "rtb_render_begin", "rtb_render_end",
            "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj", "rtb_import_obj_ex",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
@@ -127,6 +127,10 @@ def lib():
         L.rtb_free.argtypes = [vp]; L.rtb_free.restype = None
         L.rtb_free_pinned.argtypes = [vp]; L.rtb_free_pinned.restype = None
         L.rtb_import_obj_parallel.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, vp, vp, vp]
+        L.rtb_spheres_closest_hit.argtypes = [C.c_int32, vp, C.c_uint32, vp, vp, C.c_uint64, vp, vp, vp]
+        L.rtb_spheres_bounds.argtypes = [vp, C.c_uint32, vp]; L.rtb_spheres_bounds.restype = None
+        L.rtb_gen_random_spheres.argtypes = [C.c_uint64, vp, vp]; L.rtb_gen_random_spheres.restype = C.c_uint32
+        L.rtb_gen_random_triangles.argtypes = [C.c_uint64, vp, vp]; L.rtb_gen_random_triangles.restype = C.c_uint32
         L.rtb_fill_samples.argtypes = [C.c_uint64, C.c_uint32, vp]; L.rtb_fill_samples.restype = None
         L.rtb_write_png.argtypes = [C.c_char_p, vp, C.c_uint32, C.c_uint32]
         L.rtb_last_error.restype = C.c_char_p
@@ -472,6 +476,37 @@ def render_sequence_multi(scenes, poses, frames=None, png_pattern=None, **kw):
     _check(lib().rtb_render_sequence_multi(_scene_array(scenes), len(scenes), C.byref(p), arr, n, _ptr(frames),
                                            os.fsencode(png_pattern) if png_pattern else None, C.byref(st)))
     return frames, st.as_dict()
+
+
+# ---- the Sphere primitive and the random scene generators (dead code in the reference; see include/rtb200.h) ----
+def spheres_closest_hit(spheres_xyzr, origins, dirs, device=0):
+    """rtb_spheres_closest_hit -> (idx int32 [-1 = none], t float32, normal float32 [n, 3])"""
+    sp = np.ascontiguousarray(spheres_xyzr, np.float32).reshape(-1, 4)
+    o = np.ascontiguousarray(origins, np.float32).reshape(-1, 3); d = np.ascontiguousarray(dirs, np.float32).reshape(-1, 3)
+    t = np.zeros(len(o), np.float32); idx = np.zeros(len(o), np.int32); nrm = np.zeros((len(o), 3), np.float32)
+    _check(lib().rtb_spheres_closest_hit(device, _ptr(sp), len(sp), _ptr(o), _ptr(d), len(o), _ptr(t), _ptr(idx), _ptr(nrm)))
+    return idx, t, nrm
+
+
+def spheres_bounds(spheres_xyzr):
+    sp = np.ascontiguousarray(spheres_xyzr, np.float32).reshape(-1, 4)
+    out = np.zeros((len(sp), 6), np.float32)
+    lib().rtb_spheres_bounds(_ptr(sp), len(sp), _ptr(out))
+    return out
+
+
+def gen_random_spheres(seed):
+    """gen_random_spheres (src/main.rs:43-67) from an explicit seed -> (spheres [1, 4] {x, y, z, radius}, colors [1, 3])"""
+    sp, col = np.zeros((1, 4), np.float32), np.zeros((1, 3), np.float32)
+    n = lib().rtb_gen_random_spheres(int(seed), _ptr(sp), _ptr(col))
+    return sp[:n], col[:n]
+
+
+def gen_random_triangles(seed):
+    """gen_random_triangles (src/main.rs:69-99) from an explicit seed -> (verts [10, 9], colors [10, 3])"""
+    v, col = np.zeros((10, 9), np.float32), np.zeros((10, 3), np.float32)
+    n = lib().rtb_gen_random_triangles(int(seed), _ptr(v), _ptr(col))
+    return v[:n], col[:n]
 
 
 def measure_peaks(device=0, hbm=True):

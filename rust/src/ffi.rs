@@ -122,6 +122,11 @@ extern "C" {
     pub fn rtb_import_obj_parallel(path: *const c_char, n_threads: u32, flags: u32, verts_out: *mut *mut f32, n_out: *mut u32,
                                    stats: *mut RtbImportStats) -> i32;
     pub fn rtb_free_pinned(p: *mut c_void);
+    pub fn rtb_spheres_closest_hit(device: i32, spheres_xyzr: *const f32, n_spheres: u32, origins: *const f32, dirs: *const f32,
+                                   n_rays: u64, t_out: *mut f32, idx_out: *mut i32, normal_out: *mut f32) -> i32;
+    pub fn rtb_spheres_bounds(spheres_xyzr: *const f32, n: u32, boxes6_out: *mut f32);
+    pub fn rtb_gen_random_spheres(seed: u64, spheres_xyzr_out: *mut f32, colors_out: *mut f32) -> u32;
+    pub fn rtb_gen_random_triangles(seed: u64, verts_out: *mut f32, colors_out: *mut f32) -> u32;
     pub fn rtb_free(p: *mut c_void);
     pub fn rtb_fill_samples(seed: u64, n_pairs: u32, out: *mut f32);
     pub fn rtb_write_png(path: *const c_char, rgb8: *const u8, width: u32, height: u32) -> i32;

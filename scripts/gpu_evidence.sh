@@ -6,18 +6,7 @@ mkdir -p gpurun_out
 for C in 3 3b 4 5; do
   timeout 900 python bench.py --config $C --steps 8 > gpurun_out/r2_bench_c${C}_1gpu.json 2> gpurun_out/r2_bench_c${C}_1gpu.err; echo "bench $C rc=$?"
 done
-python scripts/profile_frame.py 3840 2160 16 3 > gpurun_out/plain3.log 2>&1 || { tail -5 gpurun_out/plain3.log; exit 1; }
-for spec in k_primary:13 k_shadow_grid:12 k_shade:12; do
-  K=${spec%%:*}; S=${spec##*:}
-  timeout 600 ncu --set full --clock-control none --import-source on -k regex:"^void $K<" -s $S -c 1 -f -o gpurun_out/r2_$K \
-      python scripts/profile_frame.py 3840 2160 16 3 > gpurun_out/ncu_$K.log 2>&1; echo "ncu $K rc=$?"
-done
-python scripts/profile_frame.py 3840 2160 16 3 576 > gpurun_out/plain3b.log 2>&1 &&
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"^void k_shadow_grid<" -s 12 -c 1 -f -o gpurun_out/r2_k_shadow_grid_c3b \
-    python scripts/profile_frame.py 3840 2160 16 3 576 > gpurun_out/ncu_sg3b.log 2>&1; echo "ncu 3b rc=$?"
-python scripts/profile_frame.py 3840 2160 1 3 288 8 > gpurun_out/plain4.log 2>&1 &&
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"^void k_shadow_grid<" -s 2 -c 1 -f -o gpurun_out/r2_k_shadow_grid_c4 \
-    python scripts/profile_frame.py 3840 2160 1 3 288 8 > gpurun_out/ncu_sg4.log 2>&1; echo "ncu 4 rc=$?"
+bash scripts/gpu_ncu_r2.sh
 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/r2_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1; echo "launch list rc=$?"

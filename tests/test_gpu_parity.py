@@ -723,3 +723,26 @@ def test_parallel_import_into_pinned_memory_and_white_default(rtb, gpu_big_bunny
     fa, sa = a.render(**kw); fb, sb = b.render(**kw)
     assert (fa == fb).all() and sa["primary_hits"] == sb["primary_hits"] > 0
     del a, v                                                          # frees the pinned array after the scene that copied it
+
+
+def test_sphere_primitive_bit_exact(rtb):
+    """SURVEY 8f-4: rtb_spheres_closest_hit (sphere.rs:50-84 intersect, :90-94 normal, Ray::new normalisation) == the oracle's
+    restatement bit for bit: 20 000 rays against 48 random spheres -- origins outside, inside and far away, directions not
+    normalised -- and the generator's own sphere seen from the reference camera."""
+    rng = np.random.default_rng(11)
+    sp = np.concatenate([rng.uniform(-50, 50, (48, 3)), rng.uniform(1, 25, (48, 1))], axis=1).astype(np.float32)
+    n = 20000
+    o = rng.uniform(-80, 80, (n, 3)).astype(np.float32)
+    o[: n // 8] = sp[rng.integers(0, 48, n // 8), :3] + rng.uniform(-0.5, 0.5, (n // 8, 3)).astype(np.float32)      # inside a sphere
+    d = (rng.uniform(-1, 1, (n, 3)) * rng.uniform(0.01, 100, (n, 1))).astype(np.float32)
+    d[n // 2:] = (sp[rng.integers(0, 48, n - n // 2), :3] - o[n // 2:]) * np.float32(0.37)                               # aimed at a centre
+    idx, t, nrm = rtb.spheres_closest_hit(sp, o, d)
+    widx, wt, wn = O.spheres_closest(sp, o, d)
+    assert (idx >= 0).sum() > n // 2 and (idx < 0).sum() > n // 10
+    assert (idx == widx).all()
+    hit = idx >= 0
+    assert (t[hit].view(np.uint32) == wt[hit].view(np.uint32)).all()
+    assert (nrm[hit].view(np.uint32) == wn[hit].view(np.uint32)).all()
+    gs, _ = rtb.gen_random_spheres(3)
+    i1, t1, n1 = rtb.spheres_closest_hit(gs, [[0, 0, 0]], [[0, 0, -1]])
+    assert i1[0] == 0 and t1[0] == np.float32(1000) - gs[0, 3] and (n1[0] == [0, 0, 1]).all()

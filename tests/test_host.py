@@ -281,3 +281,37 @@ def test_import_obj_parallel_equals_the_serial_readers(rtb, tmp_path):
     got, st = rtb.import_obj_parallel(str(out), n_threads=8)
     want = S.instanced_bunnies(3)[0][:-1]
     assert got.shape == want.shape and (got.view(np.uint32) == want.view(np.uint32)).all()
+
+
+def test_sphere_oracle_known_answers_and_generators():
+    """the Sphere primitive of the oracle against hand-derived answers (src/tracer/primitives/sphere.rs:50-84: the
+    returned value is the distance origin -> hit point), its box and normal, and the library's generators (src/main.rs:43-99:
+    counts, ranges, order of draws, reproducible from the seed)."""
+    import rtb200
+    from oracle import oracle as O
+    f = np.float32
+    # through the centre from outside: distance - radius; pointing away: None (tca < 0); grazing: d2 == radius^2
+    assert O.sphere_intersect([0, 0, -1000], 450, [0, 0, 0], [0, 0, -1]) == 550.0
+    assert O.sphere_intersect([0, 0, -1000], 450, [0, 0, 0], [0, 0, 1]) is None
+    assert O.sphere_intersect([0, 3, -10], 3, [0, 0, 0], [0, 0, -2]) == 10.0
+    assert O.sphere_intersect([0, 3.0001, -10], 3, [0, 0, 0], [0, 0, -1]) is None
+    # origin inside: t0 < 0, the far root (sphere.rs:73-78)
+    assert O.sphere_intersect([0, 0, 0], 2, [0, 0, 0.5], [0, 0, -3]) == 2.5
+    # off-axis 3-4-5: centre (0, 0, -5), radius 3, direction (0, 0.6, -0.8) is tangent (d2 = 9); the step-by-step float32 value
+    l = np.array([0, 0, -5], f); d = np.array([0, 0.6, -0.8], f); d = d / np.sqrt(f(d[0] * d[0] + d[1] * d[1]) + d[2] * d[2], dtype=f)
+    tca = f(f(f(0) + l[1] * d[1]) + l[2] * d[2]); d2 = f(f(25) - f(tca * tca))
+    got = O.sphere_intersect([0, 0, -5], 3, [0, 0, 0], [0, 0.6, -0.8])
+    assert (got is None) == bool(d2 > f(9))
+    assert (O.sphere_box([1, 2, 3], 0.5) == np.array([0.5, 1.5, 2.5, 1.5, 2.5, 3.5], f)).all()
+    assert np.allclose(O.sphere_normal([0, 0, 0], [0, 3, 4]), [0, 0.6, 0.8], atol=1e-7)
+    assert (rtb200.spheres_bounds([[1, 2, 3, 0.5], [0, 0, -1000, 450]]) == np.stack([O.sphere_box([1, 2, 3], 0.5), O.sphere_box([0, 0, -1000], 450)])).all()
+    sp, col = rtb200.gen_random_spheres(7)
+    assert sp.shape == (1, 4) and (sp[0, :3] == [0, 0, -1000]).all() and 400 <= sp[0, 3] < 500 and ((col >= 0) & (col < 1)).all()
+    v, c = rtb200.gen_random_triangles(7)
+    assert v.shape == (10, 9) and c.shape == (10, 3)
+    xyz = v.reshape(10, 3, 3)
+    assert ((xyz[..., :2] >= -500) & (xyz[..., :2] < 500)).all() and ((xyz[..., 2] >= -100) & (xyz[..., 2] < -50)).all() and ((c >= 0) & (c < 1)).all()
+    assert (rtb200.gen_random_triangles(7)[0] == v).all() and not (rtb200.gen_random_triangles(8)[0] == v).all()
+    # order of draws: the sphere's radius is the first number of the stream, then r, g, b (src/main.rs:55-61)
+    u = S.make_samples(n=2, seed=7).reshape(-1)
+    assert sp[0, 3] == f(400) + f(100) * u[0] and (col[0] == u[1:4]).all()
