@@ -1,3 +1,6 @@
 #!/bin/bash
-python scripts/tri_counts.py
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+for b in 4 3 2; do
+  echo "== shadow blocks per SM $b"
+  RTB200_SHADOW_BLOCKS=$b python scripts/ab_kernels.py 3
+  RTB200_SHADOW_BLOCKS=$b python scripts/ab_kernels.py 3b
+done
