@@ -542,7 +542,7 @@ static int prefetch_samples(rtb_scene* s, const float* samples, uint32_t n_pairs
 }
 
 // Validates params, (re)builds the light-point table on `st`, fills TraceArgs.
-static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t st, TraceArgs* a, bool allow_spec = false) {
+static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t st, TraceArgs* a, bool allow_spec = false, bool take_prefetched = true) {
     if (!s || !p) return fail(RTB_ERR_ARG, "render: null argument");
     if (!s->d_samples) return fail(RTB_ERR_STATE, "render: rtb_scene_set_samples has not been called");
     if (s->pend.active) return fail(RTB_ERR_STATE, "render: a frame begun with rtb_render_begin is in flight (rtb_render_end first)");
@@ -551,6 +551,14 @@ static int prepare_args(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
     if (world > 1 && (p->band_rows == 0 || p->rank >= world)) return fail(RTB_ERR_ARG, "render: bad band ownership");
     CUDA_TRY(cudaSetDevice(s->device));
     s->grid_rebuilds = 0;
+    // a table prefetched during the previous frame (rtb_scene_set_samples_async between rtb_render_begin and rtb_render_end): its set
+    // becomes the current one for whichever render call comes next.  (Not for the redo of a frame: that renders the SAME table again.)
+    if (take_prefetched && s->alt_ready) {
+        swap_table_sets(s);
+        s->alt_ready = false;
+        CUDA_TRY(cudaStreamWaitEvent(st, s->ev_built, 0));
+        s->grid_rebuilds += s->prefetch_rebuilds; s->prefetch_rebuilds = 0;
+    }
     TableInfo ti;
     {
         const int rc = build_tables(s, p, st, allow_spec, &ti);
@@ -876,17 +884,8 @@ int rtb_peer_close(int32_t device, void* d_ptr, int32_t owner) {
 static int render_enqueue(rtb_scene* s, const rtb_render_params* p, uint8_t* h_rgb8, uint8_t* d_full, bool first, rtb_scene::Pending* pr) {
     const bool allow_spec = first && !getenv("RTB200_NO_SPEC");
     pr->p = *p; pr->h_rgb8 = h_rgb8; pr->d_full = d_full; pr->stage = nullptr; pr->rebuilds = 0;
-    // a table prefetched during the previous frame: its set becomes the current one (a redo renders the SAME table again: the
-    // prefetched one waits for the next frame)
-    if (first && s->alt_ready) {
-        CUDA_TRY(cudaSetDevice(s->device));
-        swap_table_sets(s);
-        s->alt_ready = false;
-        CUDA_TRY(cudaStreamWaitEvent(s->stream, s->ev_built, 0));
-        pr->rebuilds += s->prefetch_rebuilds; s->prefetch_rebuilds = 0;
-    }
     TraceArgs& a = pr->a;
-    int rc = prepare_args(s, p, s->stream, &a, allow_spec);
+    int rc = prepare_args(s, p, s->stream, &a, allow_spec, first);
     if (rc != RTB_OK) return rc;
     pr->rebuilds += s->grid_rebuilds;
     const size_t bytes = (size_t)a.owned_rows * a.width * 3;

@@ -3,8 +3,10 @@
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 python scripts/e2e_breakdown.py 3 1 > gpurun_out/plain_e2e3.log 2>&1 || { tail -5 gpurun_out/plain_e2e3.log; exit 1; }
-for c in 3 4; do
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:'^k_grid_(raster|sort)$' -s 6 -c 3 -f -o gpurun_out/r2_raster_c$c \
-    python scripts/e2e_breakdown.py $c 1 > gpurun_out/ncu_raster$c.log 2>&1; echo "ncu raster $c rc=$?"
-done
+# launches that match before the steady new-table loop of e2e_breakdown.py (a table's third frame rebuilds finer, the first new table
+# after that builds synchronously): 30 on config 3 (count, fill, sort per rebuild), 25 on config 4 (count, fill)
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'^k_grid_(raster|sort)$' -s 33 -c 3 -f -o gpurun_out/r2_raster_c3 \
+    python scripts/e2e_breakdown.py 3 1 > gpurun_out/ncu_raster3.log 2>&1; echo "ncu raster 3 rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:'^k_grid_(raster|sort)$' -s 27 -c 2 -f -o gpurun_out/r2_raster_c4 \
+    python scripts/e2e_breakdown.py 4 1 > gpurun_out/ncu_raster4.log 2>&1; echo "ncu raster 4 rc=$?"
 ls -la gpurun_out/*.ncu-rep
