@@ -470,8 +470,9 @@ static int build_tables(rtb_scene* s, const rtb_render_params* p, cudaStream_t s
         // 38.0 -> 33.6 ms) but cost 3 - 6 times the build: the second frame of a table orders the lists, the third rebuilds finer.
         s->grid.uses++;
         if (s->grid.uses == 2 && !s->grid.refined && !s->no_refine && s->grid.valid) {
-            s->grid.sort_at_build = true;
+            s->grid.sort_at_build = true; s->grid.generous = true;
             CUDA_TRY(rtb_grid_build(s->grid, s->d_tris, s->n_tris, s->d_light_pts, (uint32_t)need, s->grid_cell_factor * 0.4f, false, st));
+            s->grid.generous = false;
             s->grid_rebuilds++;
             s->grid.refined = true;
             if (!s->grid.valid) {                  // the finer grids did not fit: back to the build the first frames used

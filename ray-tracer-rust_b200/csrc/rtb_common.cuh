@@ -113,6 +113,7 @@ struct RtbGrid {                   // host-side owner of the light grids of one 
     // frames rendered with this build after the first (the caller counts); `refined`: rebuilt with finer cells because the table keeps
     // being reused (rtb_api.cu: build_tables)
     uint32_t uses; bool refined;
+    bool generous;                 // set by the caller before a build: larger entry cap / budget (a build for a reused table)
     bool sort_at_build;            // set by the caller before a build: run k_grid_sort with it (the frame share is large enough to repay the pass at once)
 };
 

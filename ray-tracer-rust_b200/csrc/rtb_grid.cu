@@ -1034,7 +1034,11 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
         return cudaSuccess;
     }
     const size_t CELL_CAP = 512u << 20;
-    const uint64_t ENTRY_CAP = G.entry_cap_limit ? G.entry_cap_limit : (512ull << 20);
+    // entries a build may have / should stay below.  A build for a table that keeps being reused (G.generous, set by the caller) is
+    // paid once and may spend memory: 3 Gi entries (12 GB) allowed, cells coarsened only above 2 Gi
+    const uint64_t ENTRY_CAP = G.entry_cap_limit ? G.entry_cap_limit : (G.generous ? (3072ull << 20) : (512ull << 20));
+    // (64 bunnies, same table: 12.6 ms at 320 Mi, 9.4 at 640 Mi, 7.5 at 1 Gi, 6.9 ms at 2 Gi -- 1.68 G entries, 487 M cells of 1.9 units)
+    const uint64_t BUDGET_DEFAULT = G.generous ? (2048ull << 20) : (320ull << 20);
     if (!G.ev0) { GRID_CK(cudaEventCreate(&G.ev0)); GRID_CK(cudaEventCreate(&G.ev1)); }
     GRID_CK(grid_reserve(&G.d_lights, &G.lights_cap, (size_t)n_lights));
     GRID_CK(grid_reserve(&G.d_lbounds, &G.lbounds_cap, (size_t)n_lights * 4));
@@ -1112,7 +1116,7 @@ static cudaError_t grid_build_ex(RtbGrid& G, const float4* d_tris, uint32_t n_tr
     g.speculative = 0u; g.entries_alloc = ENTRY_CAP;
     GRID_CK(cudaEventRecord(G.ev0, st));
     uint32_t h_ctl[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
-    const unsigned long long ENTRY_BUDGET = ENTRY_CAP < (320ull << 20) ? ENTRY_CAP : (320ull << 20);    // list entries one build should stay below
+    const unsigned long long ENTRY_BUDGET = ENTRY_CAP < BUDGET_DEFAULT ? ENTRY_CAP : BUDGET_DEFAULT;    // list entries one build should stay below
     // A primitive that would cover more than RTB_GRID_MAX_CELLS_PER_PRIM cells of some light's grid goes to the `big` list every
     // ray tests.  That is meant for the ground; in a wide scene (64 bunnies over 1600 x 1400 units) the stretched projections of
     // distant primitives cross the limit by the thousand at the cell size the primitives' own extent suggests.  Coarser cells
