@@ -777,6 +777,11 @@ static int run_wavefront(rtb_scene* s, TraceArgs a, bool count, cudaStream_t st,
         uint64_t n = nu * unit;
         if (base + n > pix_total) n = pix_total - base;
         a.pix_base = (uint32_t)base; a.n_pix_chunk = (uint32_t)n; a.n_pix_padded = (uint32_t)((nu * unit + 255) / 256 * 256);
+        // k_primary: two warps per 32-pixel tile, half of the pixel's rays each, where nothing else hides the kernel's tail -- a
+        // single-chunk render (band shares of 1 / 2 / 4 / 8 GPUs of the 4K / 16 spp frame: k_primary 1.84 / 0.98 / 0.42 / 0.31 ->
+        // 1.70 / 0.90 / 0.42 / 0.22 ms, but with several chunks on two streams the frame does not gain: 14.54 -> 14.6 ms; four warps:
+        // no further gain)
+        a.primary_split = (n_chunks == 1 && a.nb_ray >= 2) ? 2u : 1u;
         CUDA_TRY(cudaMemsetAsync(b.d_queue_ctl, 0, 16 * sizeof(uint32_t), cs));
         cudaEvent_t* ev = nullptr;
         if (timed && s->timed_chunks < RTB_MAX_TIMED_CHUNKS) ev = s->evp + 4 * s->timed_chunks++;

@@ -165,6 +165,7 @@ struct TraceArgs {
     unsigned long long* queue_ticket;    // (= queue_ctl + 2) next unclaimed ray of k_shadow_queue
     // term wavefront (k_shade_terms): hit points on primitives whose normal is not along y have their 100 shading terms
     // computed one warp per hit point, one lane per sample, into `terms`; k_shade then only adds them in order.
+    uint32_t primary_split;              // k_primary: warps per 32-pixel tile (1, 2 or 4), each with a run of the pixel's rays
     uint32_t* tile_slot;                 // [nb_ray][n_pix_padded / 32]: term slot of (ray r, 32-pixel tile) or RTB_TERM_NONE (k_primary)
     uint4* term_tiles;                   // per slot: {first padded pixel of the tile, r, lanes with such a hit point, -}
     float* terms;                        // [slot][channel < term_channels][lane][sample, row stride term_stride]; nullptr: off
