@@ -309,6 +309,11 @@ typedef struct {
     uint32_t threads, n_vertices;
 } rtb_import_stats;
 int rtb_import_obj_parallel(const char* path, uint32_t n_threads, uint32_t flags, float** verts_out, uint32_t* n_out, rtb_import_stats* stats);
+/* The same with materials: flags & RTB_OBJ_MTL honours `mtllib` / `usemtl` exactly as rtb_import_obj_ex does and returns kd_out (n * 3)
+ * and ks_ns_out (n * 4) beside the triangles (either may be NULL; without the flag they come back NULL and every triangle is the
+ * reference's white).  All three arrays come from the same allocator (RTB_OBJ_PINNED: rtb_free_pinned, else rtb_free). */
+int rtb_import_obj_parallel_ex(const char* path, uint32_t n_threads, uint32_t flags, float** verts_out, float** kd_out, float** ks_ns_out,
+                               uint32_t* n_out, rtb_import_stats* stats);
 void rtb_free_pinned(void* p);
 
 /* --- the Sphere primitive and the random scene generators, dead code in the reference (src/tracer/primitives/sphere.rs is

@@ -77,7 +77,7 @@ class SequenceStats(C.Structure):
         return {k: getattr(self, k) for k, _ in self._fields_}
 
 
-EXPORTS = ["rtb_spheres_closest_hit", "rtb_spheres_bounds", "rtb_gen_random_spheres", "rtb_gen_random_triangles", "rtb_import_obj_parallel", "rtb_free_pinned", "rtb_color_to_u8_static", "rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
+EXPORTS = ["rtb_import_obj_parallel_ex", "rtb_spheres_closest_hit", "rtb_spheres_bounds", "rtb_gen_random_spheres", "rtb_gen_random_triangles", "rtb_import_obj_parallel", "rtb_free_pinned", "rtb_color_to_u8_static", "rtb_scene_create", "rtb_scene_create_ex", "rtb_scene_set_samples_async", "rtb_render_multi", "rtb_scenes_set_samples",
            "rtb_render_sequence", "rtb_render_sequence_multi", "rtb_measure_peaks", "rtb_scene_destroy", "rtb_scene_get_info", "rtb_scene_set_samples", "rtb_scene_set_materials", "rtb_render", "rtb_render_begin", "rtb_render_end",
            "rtb_render_device", "rtb_render_pixels", "rtb_color_to_u8", "rtb_scene_get_tie_ranks", "rtb_scene_get_nodes", "rtb_selftest_division", "rtb_scene_get_counters", "rtb_owned_rows", "rtb_deinterleave_bands", "rtb_peer_alloc", "rtb_peer_open", "rtb_peer_close", "rtb_import_obj", "rtb_import_obj_ex",
            "rtb_free", "rtb_fill_samples", "rtb_write_png", "rtb_last_error", "rtb_version"]
@@ -127,6 +127,7 @@ def lib():
         L.rtb_free.argtypes = [vp]; L.rtb_free.restype = None
         L.rtb_free_pinned.argtypes = [vp]; L.rtb_free_pinned.restype = None
         L.rtb_import_obj_parallel.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, vp, vp, vp]
+        L.rtb_import_obj_parallel_ex.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, vp, vp, vp, vp, vp]
         L.rtb_spheres_closest_hit.argtypes = [C.c_int32, vp, C.c_uint32, vp, vp, C.c_uint64, vp, vp, vp]
         L.rtb_spheres_bounds.argtypes = [vp, C.c_uint32, vp]; L.rtb_spheres_bounds.restype = None
         L.rtb_gen_random_spheres.argtypes = [C.c_uint64, vp, vp]; L.rtb_gen_random_spheres.restype = C.c_uint32
@@ -200,21 +201,32 @@ class _HostArrayOwner:
             self.ptr = None
 
 
-def import_obj_parallel(path, n_threads=0, pinned=False):
-    """rtb_import_obj_parallel -> ((n, 9) float32 view of the library's array (page-locked if pinned), stats dict).
-    The view keeps the allocation alive; it is freed when the last reference to the array goes."""
-    verts = C.c_void_p()
+def _owned_view(ptr, n, width, pinned):
+    owner = _HostArrayOwner(ptr, pinned)
+    buf = (C.c_float * (n * width)).from_address(ptr)
+    arr = np.frombuffer(buf, dtype=np.float32).reshape(n, width).view(_OwnedArray)
+    arr._owner = owner
+    return arr
+
+
+def import_obj_parallel(path, n_threads=0, pinned=False, mtl=False):
+    """rtb_import_obj_parallel[_ex] -> ((n, 9) float32 view of the library's array (page-locked if pinned), stats dict), or with
+    mtl=True (verts, kd (n, 3), ks_ns (n, 4), stats).  The views keep the allocations alive; they are freed with the last reference."""
+    verts, kd, ks = C.c_void_p(), C.c_void_p(), C.c_void_p()
     n = C.c_uint32(0)
     st = ImportStats()
-    _check(lib().rtb_import_obj_parallel(os.fsencode(path), n_threads, RTB_OBJ_PINNED if pinned else 0, C.byref(verts), C.byref(n), C.byref(st)))
+    flags = (RTB_OBJ_PINNED if pinned else 0) | (RTB_OBJ_MTL if mtl else 0)
+    if mtl:
+        _check(lib().rtb_import_obj_parallel_ex(os.fsencode(path), n_threads, flags, C.byref(verts), C.byref(kd), C.byref(ks), C.byref(n), C.byref(st)))
+    else:
+        _check(lib().rtb_import_obj_parallel(os.fsencode(path), n_threads, flags, C.byref(verts), C.byref(n), C.byref(st)))
     stats = {k: getattr(st, k) for k, _ in ImportStats._fields_}
     if n.value == 0:
-        return np.zeros((0, 9), np.float32), stats
-    owner = _HostArrayOwner(verts.value, pinned)
-    buf = (C.c_float * (n.value * 9)).from_address(verts.value)
-    arr = np.frombuffer(buf, dtype=np.float32).reshape(n.value, 9)
-    arr = arr.view(_OwnedArray)
-    arr._owner = owner
+        z = np.zeros((0, 9), np.float32)
+        return (z, np.zeros((0, 3), np.float32), np.zeros((0, 4), np.float32), stats) if mtl else (z, stats)
+    arr = _owned_view(verts.value, n.value, 9, pinned)
+    if mtl:
+        return arr, _owned_view(kd.value, n.value, 3, pinned), _owned_view(ks.value, n.value, 4, pinned), stats
     return arr, stats
 
 

@@ -1144,23 +1144,34 @@ int rtb_deinterleave_bands(int32_t device, const void* d_staged, uint64_t stride
 }  // extern "C"
 
 // ---- parallel OBJ import into (optionally) pinned memory: the parser is host/rtb_obj_parallel.cpp, the allocator lives here -------
-int rtb_obj_parallel_core(const char*, uint32_t, void* (*)(size_t), float**, uint32_t*, rtb_import_stats*, std::string*);
+int rtb_obj_parallel_core(const char*, uint32_t, void* (*)(size_t), float**, uint32_t*, rtb_import_stats*, std::string*, float**, float**);
 static void* alloc_pinned_(size_t bytes) { void* p = nullptr; return cudaHostAlloc(&p, bytes, cudaHostAllocDefault) == cudaSuccess ? p : nullptr; }
 static void* alloc_pageable_(size_t bytes) { return malloc(bytes); }
 
-extern "C" int rtb_import_obj_parallel(const char* path, uint32_t n_threads, uint32_t flags, float** verts_out, uint32_t* n_out, rtb_import_stats* stats) {
+extern "C" int rtb_import_obj_parallel_ex(const char* path, uint32_t n_threads, uint32_t flags, float** verts_out, float** kd_out, float** ks_ns_out,
+                                          uint32_t* n_out, rtb_import_stats* stats) {
     if (!path || !verts_out || !n_out) return fail(RTB_ERR_ARG, "rtb_import_obj_parallel: null argument");
     if (stats) memset(stats, 0, sizeof(*stats));
+    if (kd_out) *kd_out = nullptr;
+    if (ks_ns_out) *ks_ns_out = nullptr;
     std::string err;
-    const bool pinned = (flags & RTB_OBJ_PINNED) != 0;
-    const int rc = rtb_obj_parallel_core(path, n_threads, pinned ? alloc_pinned_ : alloc_pageable_, verts_out, n_out, stats, &err);
+    const bool pinned = (flags & RTB_OBJ_PINNED) != 0, mtl = (flags & RTB_OBJ_MTL) != 0;
+    float *kd = nullptr, *ks = nullptr;
+    const int rc = rtb_obj_parallel_core(path, n_threads, pinned ? alloc_pinned_ : alloc_pageable_, verts_out, n_out, stats, &err,
+                                         mtl && kd_out ? &kd : nullptr, mtl && ks_ns_out ? &ks : nullptr);
     if (rc != RTB_OK) {
-        if (*verts_out) { if (pinned) cudaFreeHost(*verts_out); else free(*verts_out); }
+        float* all[3] = {*verts_out, kd, ks};
+        for (float* q : all) if (q) { if (pinned) cudaFreeHost(q); else free(q); }
         *verts_out = nullptr; *n_out = 0;
         if (pinned) cudaGetLastError();
         return fail(rc, "%s", err.c_str());
     }
+    if (kd_out) *kd_out = kd;
+    if (ks_ns_out) *ks_ns_out = ks;
     return RTB_OK;
+}
+extern "C" int rtb_import_obj_parallel(const char* path, uint32_t n_threads, uint32_t flags, float** verts_out, uint32_t* n_out, rtb_import_stats* stats) {
+    return rtb_import_obj_parallel_ex(path, n_threads, flags & ~RTB_OBJ_MTL, verts_out, nullptr, nullptr, n_out, stats);
 }
 extern "C" void rtb_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 

@@ -1,7 +1,10 @@
 // rtb_obj_parallel.cpp -- import_obj (src/main.rs:114-149) for large files: the same grammar as rtb_import_obj_ex without
 // materials (any blank runs, CR LF, comments, `v x y z [w]`, corners `a`, `a/b`, `a//c`, `a/b/c`, negative indices, polygons as
 // fans), parsed by a pool of host threads straight into ONE output array that the caller may ask to be pinned, so that
-// rtb_scene_create's upload is a single DMA.  Plain C++, no CUDA: the output allocator is passed in.
+// rtb_scene_create's upload is a single DMA.  Plain C++, no CUDA: the output allocator is passed in.  With materials
+// (RTB_OBJ_MTL, rtb_import_obj_parallel_ex) `mtllib` / `usemtl` are honoured as rtb_import_obj_ex does: the statements are collected per
+// chunk in pass 1, resolved serially in file order into (first triangle, material) switch points, and pass 3 writes every triangle's
+// Kd and {Ks, Ns} next to its vertices.
 //
 // Three passes over chunks of the file cut at line ends (one chunk per thread):
 //   1. count: `v` lines, triangles (corners - 2 per `f` line), lines            -> prefix sums give every chunk its offsets
@@ -24,12 +27,16 @@ extern "C" void rtb_set_error_(const char* msg);
 
 namespace {
 
+struct MtlEvent { bool lib; std::string name; size_t tri, line; };    // a `mtllib` / `usemtl` line: triangles of the chunk before it, line in the chunk
 struct Chunk {
     size_t b = 0, e = 0;                  // byte range [b, e): whole lines
     size_t n_v = 0, n_tri = 0, n_lines = 0;
     size_t v0 = 0, tri0 = 0, line0 = 0;   // exclusive prefix sums
+    std::vector<MtlEvent> events;         // (materials wanted)
     std::string err;                      // first error of this chunk
 };
+struct Material { std::string name; float kd[3] = {1.0f, 1.0f, 1.0f}, ks[3] = {0.0f, 0.0f, 0.0f}, ns = 0.0f; };
+struct Switch { size_t tri; Material m; };                             // from global triangle `tri` on: material m
 
 inline bool is_blank(char c) { return c == ' ' || c == '\t' || c == '\r'; }
 
@@ -75,6 +82,38 @@ inline bool parse_corner(const char* b, const char* e, size_t nv, size_t* out) {
     return true;
 }
 
+inline bool tok_is(const char* tb, const char* te, const char* w) { const size_t n = strlen(w); return (size_t)(te - tb) == n && memcmp(tb, w, n) == 0; }
+
+// newmtl / Kd / Ks / Ns of one material library, appended to mats (the grammar of rtb_import_obj_ex's parse_mtl)
+bool parse_mtl_file(const std::string& path, std::vector<Material>* mats) {
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return false;
+    std::string data; char buf[1 << 16]; size_t got;
+    while ((got = fread(buf, 1, sizeof(buf), f)) > 0) data.append(buf, got);
+    fclose(f);
+    const char* p = data.data(); const char* end = p + data.size();
+    while (p < end) {
+        const char* eol = (const char*)memchr(p, '\n', (size_t)(end - p));
+        if (!eol) eol = end;
+        const char* q = p; const char *tb, *te;
+        p = eol + 1;
+        if (!next_token(q, eol, tb, te)) continue;
+        if (tok_is(tb, te, "newmtl")) { Material m; if (next_token(q, eol, tb, te)) m.name.assign(tb, te); mats->push_back(m); continue; }
+        if (mats->empty()) continue;
+        Material& m = mats->back();
+        const bool is_kd = tok_is(tb, te, "Kd"), is_ks = tok_is(tb, te, "Ks");
+        if (is_kd || is_ks) {
+            float v[3]; bool ok = true;
+            for (int a = 0; a < 3 && ok; ++a) ok = next_token(q, eol, tb, te) && parse_float(tb, te, &v[a]);
+            if (ok) memcpy(is_kd ? m.kd : m.ks, v, sizeof(v));
+        } else if (tok_is(tb, te, "Ns")) {
+            float v;
+            if (next_token(q, eol, tb, te) && parse_float(tb, te, &v)) m.ns = v;
+        }
+    }
+    return true;
+}
+
 template <typename F>
 void for_each_line(const char* data, const Chunk& c, F&& fn) {
     const char* p = data + c.b; const char* end = data + c.e;
@@ -99,8 +138,12 @@ void run_threads(size_t n, F&& fn) {
 }  // namespace
 
 // alloc(bytes) returns the output array (pinned or pageable); on failure of the parse the caller frees it.
+// kd_out / ksns_out (either may be null): per-triangle Kd (3 floats) and {Ks, Ns} (4 floats) from `mtllib` / `usemtl`, allocated with `alloc` too.
 int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(size_t), float** verts_out, uint32_t* n_out, rtb_import_stats* st,
-                          std::string* err) {
+                          std::string* err, float** kd_out, float** ksns_out) {
+    const bool want_mtl = kd_out != nullptr || ksns_out != nullptr;
+    if (kd_out) *kd_out = nullptr;
+    if (ksns_out) *ksns_out = nullptr;
     *verts_out = nullptr; *n_out = 0;
     const auto t0 = std::chrono::steady_clock::now();
     FILE* f = fopen(path, "rb");
@@ -151,6 +194,11 @@ int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(s
                 size_t corners = 0;
                 while (next_token(p, e, tb, te)) ++corners;
                 if (corners >= 3) c.n_tri += corners - 2;                                   // (fewer: an error, reported by pass 3)
+            } else if (want_mtl && (tok_is(tb, te, "usemtl") || tok_is(tb, te, "mtllib"))) {
+                const bool lib = *tb == 'm';
+                bool any = false;
+                while (next_token(p, e, tb, te)) { c.events.push_back({lib, std::string(tb, te), c.n_tri, c.n_lines}); any = true; if (!lib) break; }
+                if (!any && !lib) c.events.push_back({false, std::string(), c.n_tri, c.n_lines});      // `usemtl` without a name
             }
             return true;
         });
@@ -158,6 +206,26 @@ int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(s
     size_t nv = 0, ntri = 0, nl = 0;
     for (Chunk& c : ch) { c.v0 = nv; c.tri0 = ntri; c.line0 = nl; nv += c.n_v; ntri += c.n_tri; nl += c.n_lines; }
     if (ntri > 0x3fffffffull) { *err = "rtb_import_obj_parallel: too many triangles"; return RTB_ERR_LIMIT; }
+    // materials: the statements in file order -> switch points (serial: a handful of lines)
+    std::vector<Switch> switches;
+    if (want_mtl) {
+        std::string dir = path;
+        const size_t slash = dir.find_last_of("/\\");
+        dir = slash == std::string::npos ? std::string() : dir.substr(0, slash + 1);
+        std::vector<Material> mats;
+        for (const Chunk& c : ch)
+            for (const MtlEvent& ev : c.events) {
+                if (ev.lib) {
+                    if (!parse_mtl_file(dir + ev.name, &mats)) { *err = std::string(path) + ": cannot read material library " + dir + ev.name; return RTB_ERR_IO; }
+                } else {
+                    bool found = false;
+                    Material cur;
+                    for (const Material& m : mats) if (m.name == ev.name) { cur = m; found = true; }
+                    if (!found) { *err = std::string(path) + ": unknown material '" + ev.name + "' at line " + std::to_string(c.line0 + ev.line); return RTB_ERR_IO; }
+                    switches.push_back({c.tri0 + ev.tri, cur});
+                }
+            }
+    }
 
     // pass 2: vertices
     std::vector<float> verts(nv * 3);
@@ -184,15 +252,25 @@ int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(s
     // pass 3: faces -> triangles (fan around the first corner), straight into the output array
     float* out = nullptr;
     const auto ta0 = std::chrono::steady_clock::now();
+    float *kd = nullptr, *ksns = nullptr;
     if (ntri) {
         out = (float*)alloc(ntri * 9 * sizeof(float));
-        if (!out) { *err = "rtb_import_obj_parallel: out of memory"; return RTB_ERR_IO; }
+        if (kd_out) kd = (float*)alloc(ntri * 3 * sizeof(float));
+        if (ksns_out) ksns = (float*)alloc(ntri * 4 * sizeof(float));
+        *verts_out = out;                                                                    // (the caller frees what was allocated, also on failure)
+        if (kd_out) *kd_out = kd;
+        if (ksns_out) *ksns_out = ksns;
+        if (!out || (kd_out && !kd) || (ksns_out && !ksns)) { *err = "rtb_import_obj_parallel: out of memory"; return RTB_ERR_IO; }
     }
     const double alloc_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - ta0).count();
     run_threads(T, [&](size_t i) {
         Chunk& c = ch[i];
         size_t seen_v = c.v0, k = c.tri0;
         std::vector<size_t> corner;
+        // the material of triangle k: the last switch point at or before it (default: white, no specular -- src/main.rs:143)
+        size_t sw = 0;
+        while (sw < switches.size() && switches[sw].tri <= k) ++sw;
+        const Material white;
         for_each_line(data.data(), c, [&](const char* p, const char* e, size_t line) {
             const char *tb, *te;
             if (!next_token(p, e, tb, te) || te - tb != 1) return true;
@@ -214,6 +292,12 @@ int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(s
             for (size_t j = 1; j + 1 < corner.size(); ++j) {
                 const size_t tri[3] = {corner[0], corner[j], corner[j + 1]};
                 for (int c3 = 0; c3 < 3; ++c3) memcpy(out + 9 * k + 3 * c3, verts.data() + 3 * tri[c3], 3 * sizeof(float));
+                if (want_mtl) {
+                    while (sw < switches.size() && switches[sw].tri <= k) ++sw;
+                    const Material& m = sw ? switches[sw - 1].m : white;
+                    if (kd) memcpy(kd + 3 * k, m.kd, sizeof(m.kd));
+                    if (ksns) { memcpy(ksns + 4 * k, m.ks, sizeof(m.ks)); ksns[4 * k + 3] = m.ns; }
+                }
                 ++k;
             }
             return true;

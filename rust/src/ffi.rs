@@ -121,6 +121,8 @@ extern "C" {
                              ks_ns_out: *mut *mut f32, n_out: *mut u32) -> i32;
     pub fn rtb_import_obj_parallel(path: *const c_char, n_threads: u32, flags: u32, verts_out: *mut *mut f32, n_out: *mut u32,
                                    stats: *mut RtbImportStats) -> i32;
+    pub fn rtb_import_obj_parallel_ex(path: *const c_char, n_threads: u32, flags: u32, verts_out: *mut *mut f32, kd_out: *mut *mut f32,
+                                      ks_ns_out: *mut *mut f32, n_out: *mut u32, stats: *mut RtbImportStats) -> i32;
     pub fn rtb_free_pinned(p: *mut c_void);
     pub fn rtb_spheres_closest_hit(device: i32, spheres_xyzr: *const f32, n_spheres: u32, origins: *const f32, dirs: *const f32,
                                    n_rays: u64, t_out: *mut f32, idx_out: *mut i32, normal_out: *mut f32) -> i32;

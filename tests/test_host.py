@@ -283,6 +283,54 @@ def test_import_obj_parallel_equals_the_serial_readers(rtb, tmp_path):
     assert got.shape == want.shape and (got.view(np.uint32) == want.view(np.uint32)).all()
 
 
+def test_import_obj_parallel_with_materials_equals_the_serial_reader(rtb, tmp_path):
+    """rtb_import_obj_parallel_ex (RTB_OBJ_MTL): triangles, Kd and {Ks, Ns} equal rtb_import_obj_ex's on the shipped model with its
+    .mtl and on a file whose `usemtl` / `mtllib` statements fall on either side of every chunk boundary; the errors are the serial
+    reader's."""
+    path = os.path.join(S.MODELS, "big_bunny.obj")
+    wv, wkd, wks = rtb.import_obj_ex(path, mtl=True)
+    for t in (1, 3, 16):
+        v, kd, ks, st = rtb.import_obj_parallel(path, n_threads=t, mtl=True)
+        assert (v.view(np.uint32) == wv.view(np.uint32)).all() and (kd == wkd).all() and (ks == wks).all(), t
+    # without the flag: no material arrays, white by convention
+    assert len(rtb.import_obj_parallel(path, n_threads=2)) == 2
+    # several materials, two libraries, switches everywhere
+    (tmp_path / "a.mtl").write_text("newmtl red\nKd 1 0 0\nKs 0.5 0.5 0.5\nNs 10\n\nnewmtl green\nKd 0 1 0\n")
+    (tmp_path / "b.mtl").write_text("# second library\nnewmtl blue\r\nKd 0 0 1\r\nNs 3.5\r\n")
+    rng = np.random.default_rng(5)
+    lines = ["mtllib a.mtl"]
+    nv = 0
+    names = ["red", "green", "blue"]
+    for k in range(6000):
+        if k == 2500:
+            lines.append("mtllib b.mtl")
+        for _ in range(3):
+            x, y, z = rng.uniform(-10, 10, 3)
+            lines.append("v %.6f %.6f %.6f" % (x, y, z)); nv += 1
+        if k % 37 == 1:
+            lines.append("usemtl " + names[(k // 37) % (3 if k >= 2500 else 2)])
+        lines.append("f %d %d %d" % (nv - 2, nv - 1, nv) if k % 2 else "f -3 -2 -1")
+        if k % 500 == 499:
+            lines.append("f %d %d %d %d" % (nv - 3, nv - 2, nv - 1, nv))            # a quad: two triangles of the current material
+    obj = tmp_path / "multi.obj"
+    obj.write_text("\n".join(lines) + "\n")
+    wv, wkd, wks = rtb.import_obj_ex(str(obj), mtl=True)
+    assert len(wv) == 6024 and len(np.unique(wkd, axis=0)) == 4                     # white before the first usemtl, then three colours
+    for t in (1, 2, 5, 13):
+        v, kd, ks, st = rtb.import_obj_parallel(str(obj), n_threads=t, mtl=True)
+        assert st["threads"] == t
+        assert (v.view(np.uint32) == wv.view(np.uint32)).all() and (kd == wkd).all() and (ks == wks).all(), t
+    bad = tmp_path / "bad.obj"
+    bad.write_text("\n".join(lines[:9000] + ["usemtl nosuch"] + lines[9000:]) + "\n")
+    with pytest.raises(rtb.RtbError, match="unknown material 'nosuch' at line 9001"):
+        rtb.import_obj_parallel(str(bad), n_threads=4, mtl=True)
+    with pytest.raises(rtb.RtbError, match="unknown material 'nosuch' at line 9001"):
+        rtb.import_obj_ex(str(bad), mtl=True)
+    bad.write_text("mtllib missing.mtl\nv 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n")
+    with pytest.raises(rtb.RtbError, match="cannot read material library"):
+        rtb.import_obj_parallel(str(bad), n_threads=1, mtl=True)
+
+
 def test_sphere_oracle_known_answers_and_generators():
     """the Sphere primitive of the oracle against hand-derived answers (src/tracer/primitives/sphere.rs:50-84: the
     returned value is the distance origin -> hit point), its box and normal, and the library's generators (src/main.rs:43-99:
