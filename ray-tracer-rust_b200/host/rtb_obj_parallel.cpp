@@ -6,6 +6,7 @@
 // chunk in pass 1, resolved serially in file order into (first triangle, material) switch points, and pass 3 writes every triangle's
 // Kd and {Ks, Ns} next to its vertices.
 //
+// The file is mapped and parsed in place (no copy of the text).
 // Three passes over chunks of the file cut at line ends (one chunk per thread):
 //   1. count: `v` lines, triangles (corners - 2 per `f` line), lines            -> prefix sums give every chunk its offsets
 //   2. vertices: every chunk parses its `v` lines into the shared vertex array  (std::from_chars: correctly rounded, like
@@ -15,6 +16,9 @@
 #include "../../include/rtb200.h"
 
 #include <charconv>
+#include <memory>
+#include <new>
+#include <sys/mman.h>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -156,22 +160,36 @@ int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(s
     if (T == 0) T = 1;
     if (T > 256) T = 256;
     if (size < (size_t)T * 4096) T = (unsigned)(size / 4096 + 1);
-    std::vector<char> data(size + 1);
-    {   // every thread reads its share of the file (page cache -> buffer copies in parallel)
-        const int fd = fileno(f);
-        bool ok = true;
-        run_threads(T, [&](size_t i) {
-            size_t b = size * i / T, e = size * (i + 1) / T;
-            FILE* g = i == 0 ? f : fopen(path, "rb");
-            if (!g) { ok = false; return; }
-            if (fseek(g, (long)b, SEEK_SET) != 0 || fread(data.data() + b, 1, e - b, g) != e - b) ok = false;
-            if (i != 0) fclose(g);
-        });
-        (void)fd;
-        fclose(f);
-        if (!ok) { *err = std::string("short read of ") + path; return RTB_ERR_IO; }
+    // The text is parsed where the page cache holds it: the file is mapped, not copied (a private read-only mapping; the parsing
+    // threads take the page faults of their own chunks).  Copying it into a buffer first, even with one reader per chunk, cost as
+    // much as parsing it.  A file that cannot be mapped (a pipe, an odd file system) is read into memory instead.
+    struct Text {
+        const char* p = nullptr; size_t n = 0; bool mapped = false; std::unique_ptr<char[]> owned;
+        ~Text() { if (mapped && p) munmap(const_cast<char*>(p), n); }
+    } text;
+    text.n = size;
+    if (size) {
+        void* m = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fileno(f), 0);
+        if (m != MAP_FAILED) {
+            text.p = (const char*)m; text.mapped = true;
+            madvise(m, size, MADV_WILLNEED);
+        } else {
+            text.owned.reset(new (std::nothrow) char[size]);
+            if (!text.owned) { fclose(f); *err = "rtb_import_obj_parallel: out of memory"; return RTB_ERR_IO; }
+            bool ok = true;
+            run_threads(T, [&](size_t i) {      // every thread reads its share of the file (page cache -> buffer copies in parallel)
+                size_t b = size * i / T, e = size * (i + 1) / T;
+                FILE* g = i == 0 ? f : fopen(path, "rb");
+                if (!g) { ok = false; return; }
+                if (fseek(g, (long)b, SEEK_SET) != 0 || fread(text.owned.get() + b, 1, e - b, g) != e - b) ok = false;
+                if (i != 0) fclose(g);
+            });
+            if (!ok) { fclose(f); *err = std::string("short read of ") + path; return RTB_ERR_IO; }
+            text.p = text.owned.get();
+        }
     }
-    data[size] = '\n';
+    fclose(f);
+    const char* const data = text.p;
     const auto t1 = std::chrono::steady_clock::now();
 
     std::vector<Chunk> ch(T);
@@ -185,7 +203,7 @@ int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(s
     // pass 1: counts
     run_threads(T, [&](size_t i) {
         Chunk& c = ch[i];
-        for_each_line(data.data(), c, [&](const char* p, const char* e, size_t) {
+        for_each_line(data, c, [&](const char* p, const char* e, size_t) {
             ++c.n_lines;
             const char *tb, *te;
             if (!next_token(p, e, tb, te)) return true;
@@ -232,7 +250,7 @@ int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(s
     run_threads(T, [&](size_t i) {
         Chunk& c = ch[i];
         size_t k = c.v0;
-        for_each_line(data.data(), c, [&](const char* p, const char* e, size_t line) {
+        for_each_line(data, c, [&](const char* p, const char* e, size_t line) {
             const char *tb, *te;
             if (!next_token(p, e, tb, te) || te - tb != 1 || *tb != 'v') return true;
             float xyz[3];
@@ -271,7 +289,7 @@ int rtb_obj_parallel_core(const char* path, uint32_t n_threads, void* (*alloc)(s
         size_t sw = 0;
         while (sw < switches.size() && switches[sw].tri <= k) ++sw;
         const Material white;
-        for_each_line(data.data(), c, [&](const char* p, const char* e, size_t line) {
+        for_each_line(data, c, [&](const char* p, const char* e, size_t line) {
             const char *tb, *te;
             if (!next_token(p, e, tb, te) || te - tb != 1) return true;
             if (*tb == 'v') { ++seen_v; return true; }

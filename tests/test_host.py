@@ -272,6 +272,11 @@ def test_import_obj_parallel_equals_the_serial_readers(rtb, tmp_path):
         rtb.import_obj_parallel(str(bad), n_threads=6)
     with pytest.raises(rtb.RtbError, match="Not a valid path"):
         rtb.import_obj_parallel(str(tmp_path / "missing.obj"))
+    # an empty file; a last line without a line end (the text is parsed from a mapping of the file: nothing follows its last byte)
+    (tmp_path / "empty.obj").write_bytes(b"")
+    assert rtb.import_obj_parallel(str(tmp_path / "empty.obj"))[0].shape == (0, 9)
+    (tmp_path / "nonl.obj").write_bytes(b"v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3")
+    assert (rtb.import_obj_parallel(str(tmp_path / "nonl.obj"))[0] == rtb.import_obj_ex(str(tmp_path / "nonl.obj"), mtl=False)[0]).all()
     # 3 x 3 flattened copies written by the instancing tool == the numpy construction of SURVEY 8d config 4
     tool = os.path.join(ROOT, "ray-tracer-rust_b200", "obj_instances")
     if not os.path.exists(tool):
